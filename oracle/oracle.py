@@ -1,0 +1,149 @@
+"""ctypes wrapper around librbd_oracle.so (see rbd_oracle.c for reference citations)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_dp = ctypes.POINTER(ctypes.c_double)
+_ip = ctypes.POINTER(ctypes.c_int)
+
+
+def build_oracle(force=False):
+    so = os.path.join(_DIR, "librbd_oracle.so")
+    src = os.path.join(_DIR, "rbd_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        # -march=native binaries do not travel between hosts: rebuild when the source is newer
+        subprocess.check_call(["make", "-C", _DIR, "-B", "librbd_oracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def _lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_DIR, "librbd_oracle.so")
+        try:
+            build_oracle()
+            L = ctypes.CDLL(so)
+            L.rbd_max_threads()
+        except Exception:
+            build_oracle(force=True)
+            L = ctypes.CDLL(so)
+        L.rbd_model_create.restype = ctypes.c_void_p
+        L.rbd_model_create.argtypes = [ctypes.c_int, _ip, _ip, _dp, _dp, _dp, _dp, _dp, _dp]
+        L.rbd_model_free.argtypes = [ctypes.c_void_p]
+        L.rbd_max_threads.restype = ctypes.c_int
+        _LIB = L
+    return _LIB
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def _arr(x):
+    return np.ascontiguousarray(x, dtype=np.float64)
+
+
+class Oracle:
+    def __init__(self, robot):
+        L = _lib()
+        t = robot.numeric_tables()
+        self.n = n = int(t["n"])
+        self._keep = [np.ascontiguousarray(t[k], dtype=np.float64) for k in ("X0", "Xs", "Xc", "Xq", "I", "damping")]
+        par = np.ascontiguousarray(t["parent"], dtype=np.int32)
+        sind = np.ascontiguousarray(t["S_ind"], dtype=np.int32)
+        self._h = ctypes.c_void_p(
+            L.rbd_model_create(n, par.ctypes.data_as(_ip), sind.ctypes.data_as(_ip), *[_d(a) for a in self._keep])
+        )
+        if not self._h:
+            raise RuntimeError("rbd_model_create failed (n too large?)")
+        self.L = L
+
+    def __del__(self):
+        try:
+            self.L.rbd_model_free(self._h)
+        except Exception:
+            pass
+
+    @staticmethod
+    def max_threads():
+        return int(_lib().rbd_max_threads())
+
+    # ---------------------------------------------------------------- single knot
+    def rnea(self, q, qd, qdd=None, gravity=9.81):
+        n = self.n
+        q, qd = _arr(q), _arr(qd)
+        c = np.zeros(n); v = np.zeros((n, 6)); a = np.zeros((n, 6)); f = np.zeros((n, 6))
+        qddp = _d(_arr(qdd)) if qdd is not None else None
+        self.L.rbd_rnea(self._h, _d(q), _d(qd), qddp, ctypes.c_double(gravity), _d(c), _d(v), _d(a), _d(f))
+        return c, v.T.copy(), a.T.copy(), f.T.copy()  # (6,n) like the reference
+
+    def minv(self, q):
+        n = self.n
+        M = np.zeros((n, n))
+        self.L.rbd_minv(self._h, _d(_arr(q)), _d(M))
+        return M
+
+    def rnea_grad(self, q, qd, qdd=None, gravity=9.81):
+        n = self.n
+        out = np.zeros((n, 2 * n))
+        qddp = _d(_arr(qdd)) if qdd is not None else None
+        self.L.rbd_rnea_grad(self._h, _d(_arr(q)), _d(_arr(qd)), qddp, ctypes.c_double(gravity), _d(out))
+        return out
+
+    def fd(self, q, qd, u, gravity=9.81):
+        out = np.zeros(self.n)
+        self.L.rbd_fd(self._h, _d(_arr(q)), _d(_arr(qd)), _d(_arr(u)), ctypes.c_double(gravity), _d(out))
+        return out
+
+    def fd_grad(self, q, qd, u, gravity=9.81):
+        n = self.n
+        out = np.zeros((n, 2 * n))
+        self.L.rbd_fd_grad(self._h, _d(_arr(q)), _d(_arr(qd)), _d(_arr(u)), ctypes.c_double(gravity), _d(out))
+        return out
+
+    def aba(self, q, qd, tau, gravity=9.81):
+        out = np.zeros(self.n)
+        self.L.rbd_aba(self._h, _d(_arr(q)), _d(_arr(qd)), _d(_arr(tau)), ctypes.c_double(gravity), _d(out))
+        return out
+
+    def crba(self, q):
+        n = self.n
+        M = np.zeros((n, n))
+        self.L.rbd_crba(self._h, _d(_arr(q)), _d(M))
+        return M
+
+    # -------------------------------------------------------------------- batched
+    # x: (B, stride) fp64, packed [q | qd | u-or-qdd]; outputs use the GPU layouts
+    def _batch(self, fn, x, out_per_knot, *extra, nthreads=0):
+        x = _arr(x)
+        B, stride = x.shape
+        out = np.zeros((B, out_per_knot))
+        fn(self._h, ctypes.c_int(B), _d(x), ctypes.c_int(stride), *extra, _d(out), ctypes.c_int(nthreads))
+        return out
+
+    def batch_fd_grad(self, x, gravity=9.81, nthreads=0):
+        return self._batch(self.L.rbd_batch_fd_grad, x, 2 * self.n * self.n, ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_rnea_grad(self, x, use_qdd=True, gravity=9.81, nthreads=0):
+        return self._batch(self.L.rbd_batch_rnea_grad, x, 2 * self.n * self.n, ctypes.c_int(int(use_qdd)),
+                           ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_rnea(self, x, use_qdd=True, gravity=9.81, nthreads=0):
+        return self._batch(self.L.rbd_batch_rnea, x, self.n, ctypes.c_int(int(use_qdd)), ctypes.c_double(gravity),
+                           nthreads=nthreads)
+
+    def batch_minv(self, x, nthreads=0):
+        return self._batch(self.L.rbd_batch_minv, x, self.n * self.n, nthreads=nthreads)
+
+    def batch_fd(self, x, gravity=9.81, nthreads=0):
+        return self._batch(self.L.rbd_batch_fd, x, self.n, ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_aba(self, x, gravity=9.81, nthreads=0):
+        return self._batch(self.L.rbd_batch_aba, x, self.n, ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_crba(self, x, nthreads=0):
+        return self._batch(self.L.rbd_batch_crba, x, self.n * self.n, nthreads=nthreads)
