@@ -1,0 +1,278 @@
+"""GRiDCodeGenerator -- same Python surface as the reference class
+(reference GRiDCodeGenerator.py:3-63, :309-437; README.md:10-56), new back end.
+
+`GRiDCodeGenerator(robot).gen_all_code()` still writes one robot-specialised
+header `<namespace>.cuh` exposing ALGORITHM_inner / _device / _kernel / host
+functions, `robotModel<T>`, `gridData<T>`, `init_grid`, ... ; what it emits is
+no longer the reference's block-per-knot generic SIMT code but straight-line
+sm_100a code (one lane per knot point, one warp per 32-knot tile, TMA-staged
+batch I/O) produced by `gridcodegenerator_b200.emit`.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional
+
+from .emit import algos as _algos
+from .emit import header as _hdr
+from .emit.spatial import Model
+
+_CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
+
+
+class GRiDCodeGenerator:
+    # ------------------------------------------------------------------ ctor
+    def __init__(self, robotObj, DEBUG_MODE=False, NEED_PRINT_MAT=False, USE_DYNAMIC_SHARED_MEM=True,
+                 FILE_NAMESPACE="grid"):
+        self.robot = robotObj
+        self.code_str = ""
+        self.indent_level = 0
+        self.DEBUG_MODE = DEBUG_MODE
+        self.gen_print_mat = DEBUG_MODE or NEED_PRINT_MAT
+        self.use_dynamic_shared_mem_flag = True   # the tile kernels always use dynamic shared memory
+        self.file_namespace = FILE_NAMESPACE
+        if getattr(robotObj, "floating_base", False):
+            raise NotImplementedError("floating-base robots are out of scope of the B200 hot path (SURVEY.md 2.1 row 18)")
+        self.model = Model(robotObj)
+        self._bodies: Dict[str, _algos.Body] = {}
+        self._specs = {sp.fn + sp.tag: sp for sp in _hdr.specs(self.model.n)}
+
+    # ------------------------------------------------- emission core (L1 API)
+    # reference helpers/_code_generation_helpers.py:1-40 (same names, same behaviour)
+    def gen_add_code_line(self, new_code_line, add_indent_after=False):
+        self.code_str += "    " * self.indent_level + new_code_line + "\n"
+        if add_indent_after:
+            self.indent_level += 1
+
+    def gen_add_code_lines(self, new_code_lines, add_indent_after=False):
+        for line in new_code_lines:
+            self.gen_add_code_line(line)
+        if add_indent_after:
+            self.indent_level += 1
+
+    def gen_add_end_control_flow(self):
+        self.indent_level -= 1
+        self.gen_add_code_line("}")
+
+    def gen_add_end_function(self):
+        self.indent_level -= 1
+        self.gen_add_code_line("}")
+        self.gen_add_code_line("")
+
+    def gen_add_func_doc(self, func_desc, notes=[], params=[], return_val=None):
+        self.gen_add_code_line("/**")
+        self.gen_add_code_line(" * " + func_desc)
+        self.gen_add_code_line(" *")
+        for note in notes:
+            self.gen_add_code_line(" * " + note)
+        for p in params:
+            self.gen_add_code_line(" * @param " + p)
+        if return_val is not None:
+            self.gen_add_code_line(" * @return " + return_val)
+        self.gen_add_code_line(" */")
+
+    def _add_block(self, text: str):
+        ind = "    " * self.indent_level
+        for line in text.split("\n"):
+            self.code_str += (ind + line if line else "") + "\n"
+
+    # --------------------------------------------------------- body cache
+    def _body(self, name: str) -> _algos.Body:
+        if name not in self._bodies:
+            self._bodies[name] = self._specs[name].body(self.model)
+        return self._bodies[name]
+
+    def _variants(self, key: str) -> List[str]:
+        return [k for k, sp in self._specs.items() if sp.key == key]
+
+    def _temp_mem_size(self, key: str) -> int:
+        """Per-knot state elements (the reference's s_temp size plays this role)."""
+        return max(self._body(v).nslots for v in self._variants(key))
+
+    # ------------------------------------------------------ generic tiers
+    def _gen_inner(self, key: str, variants: Optional[List[str]] = None):
+        for v in variants or self._variants(key):
+            sp = self._specs[v]
+            b = self._body(v)
+            self._add_block(_hdr.emit_inner(sp, b))
+            self._add_block(_hdr.emit_algo_struct(sp, b, self.model.n))
+            self._add_block(_hdr.emit_config(sp, b, self.model.n))
+
+    def _gen_device(self, key: str, variants=None):
+        # device and kernel tiers are emitted together (the kernel is a 6-line shell around the device tier)
+        for v in variants or self._variants(key):
+            self._add_block(_hdr.emit_device_and_kernel(self._specs[v], self.model.n))
+
+    def _gen_kernel(self, key: str, variants=None):
+        for v in variants or self._variants(key):
+            self._add_block(_hdr.emit_launch(self._specs[v], self.model.n))
+
+    def _gen_host(self, key: str, mode: int = 0):
+        for hs in _hdr.host_specs(self.model.n):
+            if hs.fn == key:
+                self._add_block(_hdr.emit_host(hs, mode))
+
+    def _gen_algo(self, key: str):
+        """inner -> device/kernel -> launcher -> host x3, like the reference's gen_<algo> drivers
+        (e.g. algorithms/_inverse_dynamics.py:514-533)."""
+        self._gen_inner(key)
+        self._gen_device(key)
+        self._gen_kernel(key)
+        for mode in (0, 1, 2):
+            self._gen_host(key, mode)
+
+
+def _bind(key: str):
+    """Create the reference's per-algorithm generator family for `key`."""
+    def temp_mem_size(self, *a, **k):
+        return self._temp_mem_size(key)
+
+    def inner(self, use_thread_group=False, **k):
+        self._gen_inner(key)
+
+    def device(self, use_thread_group=False, **k):
+        self._gen_device(key)
+
+    def kernel(self, use_thread_group=False, single_call_timing=False, **k):
+        self._gen_kernel(key)
+
+    def host(self, mode=0):
+        self._gen_host(key, mode)
+
+    def driver(self, use_thread_group=False):
+        self._gen_algo(key)
+
+    def function_call(self, *a, **k):
+        raise NotImplementedError("inner functions are per-thread straight-line code in this back end; "
+                                  "call <algo>_inner<T, NT>(o, inputs..., S, gravity) directly")
+
+    return temp_mem_size, inner, device, kernel, host, driver, function_call
+
+
+for _key in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+             "forward_dynamics_gradient"):
+    _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_inner_temp_mem_size", _t)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_inner", _i)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_device", _d)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_kernel", _k)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_host", _h)
+    setattr(GRiDCodeGenerator, f"gen_{_key}", _drv)
+    setattr(GRiDCodeGenerator, f"gen_{_key}_inner_function_call", _fc)
+# names that differ in the reference (algorithms/_forward_dynamics_gradient.py:7, :107; _inverse_dynamics.py:323)
+GRiDCodeGenerator.gen_forward_dynamics_gradient_inner_python = GRiDCodeGenerator.gen_forward_dynamics_gradient_inner
+GRiDCodeGenerator.gen_forward_dynamics_gradient_kernel_max_temp_mem_size = \
+    GRiDCodeGenerator.gen_forward_dynamics_gradient_inner_temp_mem_size
+GRiDCodeGenerator.gen_inverse_dynamics_gradient_kernel_max_temp_mem_size = \
+    GRiDCodeGenerator.gen_inverse_dynamics_gradient_inner_temp_mem_size
+GRiDCodeGenerator.gen_inverse_dynamics_device_temp_mem_size = GRiDCodeGenerator.gen_inverse_dynamics_inner_temp_mem_size
+
+
+# ----------------------------------------------------------------- file scaffolding
+from .emit import scaffold as _sc  # noqa: E402
+
+ALGO_ORDER = ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+              "forward_dynamics_gradient")
+
+
+def gen_add_includes(self, use_thread_group=False):
+    """reference GRiDCodeGenerator.py:66-84; the runtime header is inlined so grid.cuh stays standalone."""
+    self._add_block(_sc.INCLUDES)
+    with open(os.path.join(_CSRC, "grid_b200_runtime.cuh")) as f:
+        rt = f.read().replace("#pragma once\n", "")
+    self._add_block("// ---- inlined gridcodegenerator_b200/csrc/grid_b200_runtime.cuh ----\n" + rt)
+
+
+def gen_add_gpu_err(self):
+    self._add_block(_sc.GPU_ERR)
+    if self.gen_print_mat:
+        self._add_block(_sc.PRINT_MAT)
+
+
+def _scratch_constants(self):
+    per4 = per8 = 0
+    for name, sp in self._specs.items():
+        b = self._body(name)
+        IN = [e for _, e in sp.streams]
+        for size in (4, 8):
+            NT, state_smem, _ = _hdr.choose_config(max(b.nslots, 1), IN, sp.out_n(self.model.n), size)
+            if not state_smem:
+                if size == 4:
+                    per4 = max(per4, NT * b.nslots)
+                else:
+                    per8 = max(per8, NT * b.nslots)
+    return per4, per8
+
+
+def gen_add_constants_helpers(self):
+    """reference GRiDCodeGenerator.py:86-158 (same constant names; *_DYNAMIC_SHARED_MEM_COUNT is in units of T)."""
+    n = self.model.n
+    r = self.robot
+    lines = [f"const int NUM_JOINTS = {n};", f"const int NUM_VEL = {n};",
+             f"const int NUM_EES = {r.get_total_leaf_nodes()};",
+             "const int KNOTS_PER_WARP = 32;    // one lane owns one knot point",
+             "const int SUGGESTED_THREADS = 32; // single-warp CTAs: warps never synchronise with each other"]
+    per4, per8 = _scratch_constants(self)
+    lines += [f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
+              f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F64 = {per8};",
+              "const int GRID_SCRATCH_BLOCKS_PER_SM = 8;"]
+    self.gen_add_code_lines(lines)
+    self._add_block(_sc.STRUCTS)
+
+
+def gen_add_shared_mem_constants(self):
+    """<CODE>_DYNAMIC_SHARED_MEM_COUNT for T = float (reference GRiDCodeGenerator.py:97-110), emitted after the
+    algorithm configs exist."""
+    seen = {}
+    for name, sp in self._specs.items():
+        seen.setdefault(sp.code, []).append(f"{sp.fn}{sp.tag}_cfg<float>::SMEM_BYTES")
+    for code, exprs in seen.items():
+        mx = exprs[0]
+        for e in exprs[1:]:
+            mx = f"({mx} > {e} ? {mx} : {e})"
+        self.gen_add_code_line(f"const size_t {code}_DYNAMIC_SHARED_MEM_COUNT = ({mx} + sizeof(float) - 1)/sizeof(float);")
+
+
+def gen_init_close_grid(self):
+    self._add_block(_sc.LIFECYCLE)
+
+
+def gen_all_code(self, use_thread_group=False, include_base_inertia=False, include_homogenous_transforms=False,
+                 fixed_target_name=None, output_dir="."):
+    """Emit <namespace>.cuh into output_dir (reference GRiDCodeGenerator.py:309-437 writes it to the CWD)."""
+    self.code_str = ""
+    self.indent_level = 0
+    notes = ["Interface (same names as the reference GRiD header):",
+             "    __host__   robotModel<T> *d_robotModel = init_robotModel<T>()",
+             "    __host__   cudaStream_t *streams = init_grid<T>()",
+             "    __host__   gridData<T> *hd_data = init_gridData<T,NUM_TIMESTEPS>();",
+             "    __host__   close_grid<T>(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> *hd_data)",
+             "  per ALGORITHM in {inverse_dynamics, direct_minv, forward_dynamics, inverse_dynamics_gradient,",
+             "                    forward_dynamics_gradient}:",
+             "    __device__ ALGORITHM_inner<T,NT>(T *o, const T *q, ..., T *S, const T gravity)   one thread = one knot point",
+             "    __device__ ALGORITHM_device<T>(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) one warp = 32 knot points",
+             "    __global__ ALGORITHM_kernel<T>(T *d_out, const T *d_in, const int stride, ..., const robotModel<T> *, const T gravity, const int NUM_TIMESTEPS)",
+             "    __host__   ALGORITHM<T,FLAGS...>(gridData<T> *hd_data, const robotModel<T> *d_robotModel, const T gravity, const int num_timesteps, const dim3 block_dimms, const dim3 thread_dimms, cudaStream_t *streams)",
+             "    __host__   cudaError_t ALGORITHM_launch<T>(..., cudaStream_t stream)   asynchronous, no copies",
+             "", "Suggested Type T is float", "",
+             "Kernels are sm_100a only: compile with -gencode arch=compute_100a,code=sm_100a"]
+    self.gen_add_func_doc("This instance of grid.cuh is optimized for the urdf: " + self.robot.name, notes)
+    self.gen_add_code_line("#pragma once")
+    self.gen_add_includes(use_thread_group)
+    self.gen_add_gpu_err()
+    self.gen_add_code_line("namespace " + self.file_namespace + " {", True)
+    self.gen_add_constants_helpers()
+    for key in ALGO_ORDER:
+        getattr(self, "gen_" + key)(use_thread_group)
+    self.gen_add_shared_mem_constants()
+    self.gen_init_close_grid()
+    self.gen_add_end_control_flow()
+    path = os.path.join(output_dir, self.file_namespace + ".cuh")
+    with open(path, "w") as f:
+        f.write(self.code_str)
+    return path
+
+
+for _f in (gen_add_includes, gen_add_gpu_err, gen_add_constants_helpers, gen_add_shared_mem_constants,
+           gen_init_close_grid, gen_all_code):
+    setattr(GRiDCodeGenerator, _f.__name__, _f)

@@ -1,0 +1,250 @@
+// grid_b200_runtime.cuh -- hand-written sm_100a runtime shared by every emitted grid.cuh.
+//
+// Execution model (replaces the reference's "one thread block per knot point, ~40 __syncthreads per
+// knot", helpers/_code_generation_helpers.py:41-67, algorithms/_forward_dynamics_gradient.py:113-184):
+//   * one lane owns one knot point, one warp owns a tile of 32 knot points, warps never synchronise
+//     with each other (no __syncthreads anywhere);
+//   * the tile's inputs (32 x stride contiguous values of the reference's AoS batch, e.g. [q|qd|u]) are
+//     fetched by ONE TMA bulk copy (cp.async.bulk + mbarrier), double buffered so the next tile's load
+//     overlaps this tile's math; the tile's outputs are assembled in shared memory and written by ONE
+//     TMA bulk store -> HBM traffic is exactly the algorithmic bytes, fully coalesced;
+//   * per-thread pass-to-pass state lives in shared memory as S[slot*NT + tid] (conflict-free,
+//     immediate-offset LDS/STS); robots whose state does not fit use a global scratch with the same layout.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifndef GRID_BEFORE_FIRST_OUTPUT
+#define GRID_BEFORE_FIRST_OUTPUT() do { } while (0)
+#endif
+
+namespace grid_rt {
+
+__device__ __forceinline__ void grid_sincos(float x, float* s, float* c) { sincosf(x, s, c); }
+__device__ __forceinline__ void grid_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+
+constexpr int TILE = 32;          // knot points per warp tile
+constexpr int MAX_STREAMS = 3;    // input arrays per algorithm (e.g. q_qd_u, qdd, Minv)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA 1-D bulk copies (no tensor map needed: a tile of the AoS batch is one contiguous byte range)
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <typename T>
+struct TileArgs {
+    const T* in[MAX_STREAMS];   // device arrays, knot-major
+    int stride[MAX_STREAMS];    // elements between consecutive knot points
+    T* out;                     // OUT elements per knot point, contiguous
+    T* scratch;                 // global state scratch (only when the state is not in shared memory)
+    T gravity;
+    int num_knots;
+};
+
+__host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+// per-knot element count of input stream s of algorithm A (0 = stream unused)
+template <class A>
+__host__ __device__ constexpr int in_n(int s) { return s == 0 ? A::IN0 : (s == 1 ? A::IN1 : A::IN2); }
+
+// Shared-memory footprint (bytes) of one CTA of NT threads.
+template <class A, typename T, int NT, bool STATE_SMEM, bool STAGED>
+constexpr size_t tile_smem_bytes() {
+    size_t state = STATE_SMEM ? align16(size_t(A::SLOTS) * NT * sizeof(T)) : 0;
+    size_t per_warp = 0;
+    if (STAGED) {
+        for (int s = 0; s < MAX_STREAMS; s++) per_warp += 2 * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+        per_warp += align16(size_t(TILE) * A::OUT * sizeof(T));
+        per_warp += 16;  // two mbarriers
+    }
+    return state + per_warp * (NT / 32) + 16;
+}
+
+// One warp processes tiles  first, first + step, ...  of 32 knot points.
+template <class A, typename T, int NT, bool STATE_SMEM, bool STAGED>
+__device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* smem) {
+    const int tid = threadIdx.x;
+    if (tid >= NT) return;                          // extra threads of an oversized block idle
+    const int lane = tid & 31, warp = tid >> 5;
+    const int nthreads = blockDim.x < NT ? blockDim.x : NT;
+    const int nwarps = nthreads >> 5;
+    if (warp >= nwarps) return;
+    const int num_tiles = (a.num_knots + TILE - 1) / TILE;
+    const int first = blockIdx.x * nwarps + warp, step = gridDim.x * nwarps;
+
+    T* S;
+    size_t off = 0;
+    if (STATE_SMEM) {
+        S = reinterpret_cast<T*>(smem) + tid;
+        off = align16(size_t(A::SLOTS) * NT * sizeof(T));
+    } else {
+        S = a.scratch + (size_t(blockIdx.x) * NT) * A::SLOTS + tid;
+    }
+
+    if (!STAGED) {
+        for (int tile = first; tile < num_tiles; tile += step) {
+            const int k = tile * TILE + lane;
+            if (k < a.num_knots) {
+                const T* x[MAX_STREAMS];
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++) x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
+                A::template run<NT>(a.out + size_t(k) * A::OUT, x[0], x[1], x[2], S, a.gravity);
+            }
+        }
+        return;
+    }
+
+    // ---- staged path: carve this warp's buffers
+    size_t per_warp = 0, in_off[MAX_STREAMS][2];
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) { in_off[s][b] = per_warp; per_warp += align16(size_t(TILE) * in_n<A>(s) * sizeof(T)); }
+    const size_t out_off = per_warp;
+    per_warp += align16(size_t(TILE) * A::OUT * sizeof(T));
+    const size_t bar_off = per_warp;
+    per_warp += 16;
+    unsigned char* wbase = smem + off + per_warp * warp;
+    T* out_s = reinterpret_cast<T*>(wbase + out_off);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(wbase + bar_off);
+
+    // a tile can go through TMA when it is full and every stream is dense and 16-byte aligned
+    bool dense = (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++)
+        if (in_n<A>(s)) dense = dense && a.stride[s] == in_n<A>(s) && (reinterpret_cast<uintptr_t>(a.in[s]) & 15) == 0;
+
+    if (lane == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+
+    auto issue_load = [&](int tile, int buf) {      // lane 0 only
+        uint32_t bytes = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++) bytes += in_n<A>(s) ? uint32_t(TILE * in_n<A>(s) * sizeof(T)) : 0u;
+        mbar_expect_tx(&bar[buf], bytes);
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++)
+            if (in_n<A>(s))
+                bulk_g2s(wbase + in_off[s][buf], a.in[s] + size_t(tile) * TILE * in_n<A>(s),
+                         uint32_t(TILE * in_n<A>(s) * sizeof(T)), &bar[buf]);
+    };
+    auto tile_is_tma = [&](int tile) { return dense && (tile + 1) * TILE <= a.num_knots; };
+
+    uint32_t phase[2] = {0u, 0u};
+    int buf = 0;
+    bool store_pending = false;
+    if (first < num_tiles && tile_is_tma(first) && lane == 0) issue_load(first, 0);
+
+    for (int tile = first; tile < num_tiles; tile += step, buf ^= 1) {
+        const int next = tile + step;
+        const bool tma = tile_is_tma(tile);
+        if (next < num_tiles && tile_is_tma(next) && lane == 0) issue_load(next, buf ^ 1);
+        const int nvalid = min(TILE, a.num_knots - tile * TILE);
+        const T* x[MAX_STREAMS];
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++) x[s] = reinterpret_cast<const T*>(wbase + in_off[s][buf]) + lane * in_n<A>(s);
+        if (tma) {
+            mbar_wait(&bar[buf], phase[buf]);
+            phase[buf] ^= 1u;
+        } else {                                     // ragged tail / strided or unaligned caller buffers
+#pragma unroll
+            for (int s = 0; s < MAX_STREAMS; s++) {
+                if (!in_n<A>(s)) continue;
+                T* dst = reinterpret_cast<T*>(wbase + in_off[s][buf]);
+                for (int i = lane; i < nvalid * in_n<A>(s); i += 32) {
+                    const int kk = i / in_n<A>(s), e = i - kk * in_n<A>(s);
+                    dst[i] = a.in[s][(size_t(tile) * TILE + kk) * a.stride[s] + e];
+                }
+            }
+            __syncwarp();
+        }
+        if (store_pending) {                         // out_s is still being read by the previous bulk store
+            if (lane == 0) bulk_wait_read0();
+            __syncwarp();
+            store_pending = false;
+        }
+        if (lane < nvalid) A::template run<NT>(out_s + lane * A::OUT, x[0], x[1], x[2], S, a.gravity);
+        __syncwarp();
+        if (tma) {
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                bulk_s2g(a.out + size_t(tile) * TILE * A::OUT, out_s, uint32_t(TILE * A::OUT * sizeof(T)));
+                bulk_commit();
+            }
+            store_pending = true;
+        } else {
+            T* dst = a.out + size_t(tile) * TILE * A::OUT;
+            for (int i = lane; i < nvalid * A::OUT; i += 32) dst[i] = out_s[i];
+            __syncwarp();
+        }
+    }
+    if (lane == 0) bulk_wait0();                     // smem must outlive the last bulk store
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------ host side
+struct KernelPlan { const void* fn; int device; int blocks_per_sm; int sms; };
+
+// Persistent grid for a tile kernel: resident CTAs per SM (from the occupancy calculator, after opting in
+// to the large dynamic shared-memory carve-out) x SM count, clamped to the number of warp tiles.
+// Cached per (kernel, device); returns <= 0 on error (cudaGetLastError() holds the reason).
+inline int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int num_knots) {
+    static KernelPlan cache[64];
+    static int ncache = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    const KernelPlan* plan = nullptr;
+    for (int i = 0; i < ncache; i++)
+        if (cache[i].fn == fn && cache[i].device == dev) { plan = &cache[i]; break; }
+    if (!plan) {
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_bytes)) != cudaSuccess) return -1;
+        int per_sm = 0, sms = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem_bytes) != cudaSuccess) return -1;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+        if (per_sm <= 0) { per_sm = 0; }
+        if (ncache >= 64) return -1;
+        cache[ncache] = KernelPlan{fn, dev, per_sm, sms};
+        plan = &cache[ncache++];
+    }
+    if (plan->blocks_per_sm <= 0) return 0;
+    const int tiles = (num_knots + TILE - 1) / TILE;
+    const int warps_per_block = threads / 32;
+    const int want = (tiles + warps_per_block - 1) / warps_per_block;
+    const int cap = plan->blocks_per_sm * plan->sms;
+    return want < cap ? want : cap;
+}
+
+// Number of CTAs the global state scratch attached to the robot model can serve (0 = none allocated).
+inline int& scratch_blocks() { static int v = 0; return v; }
+
+}  // namespace grid_rt

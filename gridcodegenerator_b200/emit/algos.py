@@ -1,0 +1,482 @@
+"""Per-knot-point algorithm bodies, emitted as straight-line CUDA for one thread.
+
+Thread mapping (B200 design): one lane owns one knot point, one
+warp owns a tile of 32 knot points; quantities that must survive between
+passes live in a per-thread state area `S[slot*NT]` (shared memory, lane
+interleaved => conflict-free, immediate-offset addressing), everything else in
+registers.  The algorithms follow the reference's CPU oracle:
+
+  RNEA            reference _test.py:5-107      (emitted twin: algorithms/_inverse_dynamics.py:33-321)
+  direct Minv     reference _test.py:117-226    (algorithms/_direct_minv.py:23-453)
+  FD              reference _test.py:498-501    (algorithms/_forward_dynamics.py:21-115)
+  grad RNEA       reference _test.py:229-494    (algorithms/_inverse_dynamics_gradient.py:27-775)
+  grad FD         reference _test.py:496-520    (algorithms/_forward_dynamics_gradient.py:7-62)
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+from .core import Em, V, ZERO, ONE, const
+from .spatial import Model, Trig, Xform, fxv, inertia_mul, mxS, unit
+
+
+class Ctx:
+    def __init__(self, model: Model, em: Optional[Em] = None):
+        self.m = model
+        self.em = em or Em()
+        self.n = model.n
+        self.X: List[Xform] = []
+        self.q: List[V] = []
+        self.qd: List[V] = []
+        self.gravity = V(s="gravity")
+
+    # -------------------------------------------------------------- inputs
+    def read_vec(self, ptr: str, prefix: str) -> List[V]:
+        return [self.em.named(f"{prefix}{j}", f"{ptr}[{j}]") for j in range(self.n)]
+
+    def prologue(self, q_ptr: str = "q"):
+        """sin/cos of every revolute joint angle (reference helpers/_topology_helpers.py:194-195) and the
+        factored transform handles."""
+        em = self.em
+        self.q = self.read_vec(q_ptr, "q_")
+        self.X = []
+        for j, jd in enumerate(self.m.joints):
+            if jd.revolute:
+                em.line(f"T sn{j}, cs{j}; grid_sincos(q_{j}, &sn{j}, &cs{j});")
+                tr = Trig(V(s=f"sn{j}"), V(s=f"cs{j}"), self.q[j])
+            else:
+                tr = Trig(None, None, self.q[j])
+            self.X.append(Xform(jd, tr))
+
+
+class Pusher:
+    """Accumulate child -> parent contributions in a fixed order.
+
+    A contribution to the joint processed next (parent == j-1) stays in registers; any other is a
+    read-modify-write on the parent's state slots.  This replaces the reference's shared-memory atomicAdd
+    for repeated parents (algorithms/_inverse_dynamics.py:290-294) with a deterministic order."""
+
+    def __init__(self, em: Em, name, width: int = 6):
+        self.em, self.name, self.width = em, name, width
+        self.carry: Dict[int, List[V]] = {}
+        self.in_state: Dict[int, bool] = {}
+
+    def set_base(self, j: int, vec: Sequence[V]):
+        self.em.store_vec(self.name, j, vec)
+        self.in_state[j] = True
+
+    def push(self, p: int, j: int, fn):
+        """fn(acc) -> list of V computing contribution (+ acc)."""
+        em = self.em
+        if p == j - 1:
+            self.carry[p] = fn(self.carry.get(p))
+        else:
+            base = em.load_vec(self.name, p, self.width) if self.in_state.get(p) else None
+            em.store_vec(self.name, p, fn(base))
+            self.in_state[p] = True
+
+    def pull(self, j: int) -> List[V]:
+        em = self.em
+        base = em.load_vec(self.name, j, self.width) if self.in_state.get(j) else None
+        c = self.carry.pop(j, None)
+        if base is None and c is None:
+            return [ZERO] * self.width
+        if base is None:
+            return list(c)
+        if c is None:
+            return base
+        return em.vadd(base, c)
+
+
+# ====================================================================== RNEA
+def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f"):
+    """v, a, f per joint in id order (ids are topologically sorted).  f_j -> state `fname`; with `keep`
+    also v_j, I v_j and X a_parent (needed by the gradient)."""
+    em, m = cx.em, cx.m
+    V_: Dict[int, List[V]] = {}
+    A_: Dict[int, List[V]] = {}
+    grav = [ZERO] * 5 + [cx.gravity]
+    nonadj_parent = {p for j, p in enumerate(m.parent) if p >= 0 and p != j - 1}
+    for j, jd in enumerate(m.joints):
+        em.comment(f"RNEA forward, joint {j}")
+        p, S = jd.parent, jd.S
+        if p >= 0:
+            if p != j - 1:
+                vp, ap = em.load_vec("v", p), em.load_vec("a", p)
+            else:
+                vp, ap = V_[p], A_[p]
+            vJ = cx.X[j].apply(em, vp)
+            aJ = cx.X[j].apply(em, ap)
+        else:
+            vJ = [ZERO] * 6
+            aJ = cx.X[j].apply(em, grav)
+        v = list(vJ)
+        v[S] = em.add(vJ[S], qd[j])
+        a = list(aJ)
+        if qdd is not None:
+            a[S] = em.add(a[S], qdd[j])
+        if p >= 0:
+            cr = mxS(em, S, v, qd[j])
+            a = [em.add(x, y) for x, y in zip(a, cr)]
+        Iv = inertia_mul(em, jd.I, v)
+        f = fxv(em, v, Iv, acc=inertia_mul(em, jd.I, a))
+        em.store_vec(fname, j, f)
+        if keep:
+            em.store_vec("v", j, v)
+            em.store_vec("Iv", j, Iv)
+            em.store_vec("Xa", j, aJ)
+            if j in nonadj_parent:
+                em.store_vec("a", j, a)
+        elif j in nonadj_parent:
+            em.store_vec("v", j, v)
+            em.store_vec("a", j, a)
+        V_[j], A_[j] = v, a
+        V_.pop(j - 2, None)
+        A_.pop(j - 2, None)
+
+
+def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f") -> List[V]:
+    """f_parent += X^T f, c_j = S^T f_j + damping qd_j (reference _test.py:78-107)."""
+    em, m = cx.em, cx.m
+    ps = Pusher(em, fname)
+    for j in range(m.n):
+        ps.in_state[j] = True
+    c: List[V] = [ZERO] * m.n
+    for j in range(m.n - 1, -1, -1):
+        jd = m.joints[j]
+        em.comment(f"RNEA backward, joint {j}")
+        f = ps.pull(j)
+        if keep_f:
+            em.store_vec(fname, j, f)
+        c[j] = em.lincomb([(1.0, f[jd.S]), (jd.damping, qd[j])])
+        if jd.parent >= 0:
+            ps.push(jd.parent, j, lambda acc, f=f, j=j: cx.X[j].applyT(em, f, acc=acc))
+    return c
+
+
+# ================================================================ direct Minv
+def _sym_store(em: Em, name, j, M):
+    for r in range(6):
+        for k in range(r, 6):
+            em.store((name, j, r * 6 + k), M[r][k])
+
+
+def _sym_load(em: Em, name, j):
+    M = [[None] * 6 for _ in range(6)]
+    for r in range(6):
+        for k in range(r, 6):
+            M[r][k] = em.load((name, j, r * 6 + k))
+            M[k][r] = M[r][k]
+    return M
+
+
+def articulated_inertias(cx: Ctx):
+    """Backward recursion IA_p += X^T (IA - U D^-1 U^T) X (reference _test.py:117-184 without the F part,
+    algorithms/_direct_minv.py:127-148, :226-337).  Stores U_j (6) and 1/D_j in the state."""
+    em, m = cx.em, cx.m
+    carry: Dict[int, List[List[V]]] = {}
+    in_state: Dict[int, bool] = {}
+    for j in range(m.n - 1, -1, -1):
+        jd = m.joints[j]
+        em.comment(f"articulated inertia, joint {j}")
+        S, p = jd.S, jd.parent
+        IA = [[const(jd.I[r, k]) for k in range(6)] for r in range(6)]
+        extra = []
+        if in_state.get(j):
+            extra.append(_sym_load(em, "IA", j))
+        if j in carry:
+            extra.append(carry.pop(j))
+        for E in extra:
+            for r in range(6):
+                for k in range(r, 6):
+                    IA[r][k] = em.add(IA[r][k], E[r][k])
+                    IA[k][r] = IA[r][k]
+        U = [IA[r][S] for r in range(6)]
+        Dinv = em.recip(U[S])
+        em.store_vec("U", j, U)
+        em.store(("Dinv", j, 0), Dinv)
+        if p < 0:
+            continue
+        UD = [em.mul(U[r], Dinv) for r in range(6)]
+        Ia = [[None] * 6 for _ in range(6)]
+        for r in range(6):
+            for k in range(r, 6):
+                if r == S or k == S:
+                    Ia[r][k] = ZERO  # row/column S of IA - U U^T / D vanishes identically
+                else:
+                    Ia[r][k] = em.lincomb([(1.0, IA[r][k]), (-1.0, UD[r], U[k])])
+                Ia[k][r] = Ia[r][k]
+        XtIaX = cx.X[j].congruence(em, Ia)
+        if p == j - 1:
+            carry[p] = XtIaX
+        else:
+            if in_state.get(p):
+                old = _sym_load(em, "IA", p)
+                XtIaX = [[em.add(old[r][k], XtIaX[r][k]) if k >= r else None for k in range(6)] for r in range(6)]
+                for r in range(6):
+                    for k in range(r):
+                        XtIaX[r][k] = XtIaX[k][r]
+            _sym_store(em, "IA", p, XtIaX)
+            in_state[p] = True
+
+
+def minv_columns(cx: Ctx) -> Dict[tuple, V]:
+    """Minv[j][s] for j >= s, one column s at a time: the response qdd to a unit torque at joint s with zero
+    velocity and gravity (articulated-body form of the reference's F-matrix passes, _test.py:117-202).
+    Entries between different base-rooted trees are structural zeros."""
+    em, m = cx.em, cx.m
+    n = m.n
+    Minv: Dict[tuple, V] = {}
+
+    def UD(j):
+        return em.load_vec("U", j), em.load(("Dinv", j, 0))
+
+    for s in range(n):
+        em.comment(f"Minv column {s}")
+        path = [s] + sorted(m.ancestors[s], reverse=True)  # s, parent, ..., root
+        uu: Dict[int, V] = {s: ONE}
+        U, Dinv = UD(s)
+        pa = [em.mul(U[r], Dinv) for r in range(6)]
+        for idx in range(len(path) - 1):
+            j, p = path[idx], path[idx + 1]
+            pA = cx.X[j].applyT(em, pa)
+            U, Dinv = UD(p)
+            uu[p] = em.neg(pA[m.joints[p].S])
+            w = em.mul(uu[p], Dinv)
+            pa = [em.lincomb([(1.0, pA[r]), (1.0, U[r], w)]) for r in range(6)]
+        # forward: joints on the path (ancestors first), then every j > s of the same tree
+        root = path[-1]
+        tree_end = root + len(m.subtree[root])
+        todo = sorted(m.ancestors[s]) + list(range(s, tree_end))
+        acc: Dict[int, List[V]] = {}
+        needed_later = set()
+        for j in todo:
+            pj = m.parent[j]
+            if pj >= 0:
+                needed_later.add(pj)
+        for j in todo:
+            jd = m.joints[j]
+            U, Dinv = UD(j)
+            if jd.parent >= 0:
+                aJ = cx.X[j].apply(em, acc[jd.parent])
+                ua = em.dot(U, aJ)
+            else:
+                aJ = [ZERO] * 6
+                ua = ZERO
+            qddj = em.lincomb([(1.0, uu.get(j, ZERO), Dinv), (-1.0, ua, Dinv)])
+            if j >= s:
+                Minv[(j, s)] = qddj
+            if j in needed_later:
+                a = list(aJ)
+                a[jd.S] = em.add(a[jd.S], qddj)
+                acc[j] = a
+    return Minv
+
+
+def minv_get(Minv: Dict[tuple, V], r: int, c: int) -> V:
+    return Minv.get((max(r, c), min(r, c)), ZERO)
+
+
+def store_minv(cx: Ctx, Minv):
+    for (j, s), v in Minv.items():
+        cx.em.store(("Minv", j, s), v)
+
+
+def load_minv(cx: Ctx, keys) -> Dict[tuple, V]:
+    return {k: cx.em.load(("Minv", k[0], k[1])) for k in keys}
+
+
+# ===================================================================== FD
+def fd_finish(cx: Ctx, Minv, u: Sequence[V], c: Sequence[V]) -> List[V]:
+    """qdd = Minv (u - c) with symmetric indexing (reference algorithms/_forward_dynamics.py:21-50)."""
+    em, n = cx.em, cx.n
+    umc = [em.sub(u[j], c[j]) for j in range(n)]
+    return [em.lincomb([(1.0, minv_get(Minv, r, k), umc[k]) for k in range(n)]) for r in range(n)]
+
+
+# ============================================================== grad RNEA
+def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
+    """Analytical dc/dq and dc/dqd, one derivative column c at a time (both the q and the qd column of joint c
+    are carried together for ILP).  Needs v, Iv, Xa and the accumulated f in the state (rnea_forward(keep=True)
+    + rnea_backward(keep_f=True)).  Follows reference _test.py:229-488; the column of joint c touches only
+    subtree(c) (forward) and subtree(c) + ancestors(c) (backward), which is the reference's column
+    compression (algorithms/_inverse_dynamics_gradient.py:55-98) made static.
+
+    sink(c, dc_dq_col, dc_dqd_col): lists of n V's (structural zeros are constants)."""
+    em, m = cx.em, cx.m
+    n = m.n
+    for c in range(n):
+        em.comment(f"grad RNEA column {c}")
+        sub = m.subtree[c]
+        DV: Dict[int, tuple] = {}
+        ps_q, ps_d = Pusher(em, ("dfq", c)), Pusher(em, ("dfd", c))
+        last = sub[-1]
+        for j in sub:
+            jd = m.joints[j]
+            S = jd.S
+            v = em.load_vec("v", j)
+            Iv = em.load_vec("Iv", j)
+            if j == c:
+                Xa = em.load_vec("Xa", j)
+                dvq = mxS(em, S, v) if jd.parent >= 0 else [ZERO] * 6     # MxXv == Mxv since S x S = 0
+                dvd = unit(S, ONE)
+                daq = [em.add(x, y) for x, y in zip(mxS(em, S, dvq, qd[j]), mxS(em, S, Xa))]
+                dad = mxS(em, S, v)                                         # mxS(S) qd = 0
+            else:
+                pdvq, pdvd, pdaq, pdad = DV[jd.parent]
+                dvq = cx.X[j].apply(em, pdvq)
+                dvd = cx.X[j].apply(em, pdvd)
+                daq = [em.add(x, y) for x, y in zip(cx.X[j].apply(em, pdaq), mxS(em, S, dvq, qd[j]))]
+                dad = [em.add(x, y) for x, y in zip(cx.X[j].apply(em, pdad), mxS(em, S, dvd, qd[j]))]
+            if m.children[j]:
+                DV[j] = (dvq, dvd, daq, dad)
+            # df = dv x* Iv + I da + v x* (I dv)      (reference _test.py:389-424)
+            dfq = fxv(em, v, inertia_mul(em, jd.I, dvq), acc=fxv(em, dvq, Iv, acc=inertia_mul(em, jd.I, daq)))
+            dfd = fxv(em, v, inertia_mul(em, jd.I, dvd), acc=fxv(em, dvd, Iv, acc=inertia_mul(em, jd.I, dad)))
+            if j == last and not m.children[j]:
+                ps_q.carry[j], ps_d.carry[j] = dfq, dfd   # consumed immediately by the backward sweep
+            else:
+                ps_q.set_base(j, dfq)
+                ps_d.set_base(j, dfd)
+        dcq: List[V] = [ZERO] * n
+        dcd: List[V] = [ZERO] * n
+        rel = sorted(set(sub) | set(m.ancestors[c]), reverse=True)
+        for j in rel:
+            jd = m.joints[j]
+            fq, fd_ = ps_q.pull(j), ps_d.pull(j)
+            dcq[j] = fq[jd.S]
+            dcd[j] = fd_[jd.S] if j != c else em.lincomb([(1.0, fd_[jd.S])], const(jd.damping))
+            if jd.parent >= 0:
+                if j == c:
+                    Mxf = mxS(em, jd.S, em.load_vec("f", j))
+                    fq = [em.sub(x, y) for x, y in zip(fq, Mxf)]             # - X^T mxS(f) (reference :434-437)
+                ps_q.push(jd.parent, j, lambda acc, f=fq, j=j: cx.X[j].applyT(em, f, acc=acc))
+                ps_d.push(jd.parent, j, lambda acc, f=fd_, j=j: cx.X[j].applyT(em, f, acc=acc))
+        for j in rel:
+            em.release_vec(("dfq", c), j)
+            em.release_vec(("dfd", c), j)
+        sink(c, dcq, dcd)
+
+
+# ============================================================ kernel bodies
+def _out(em: Em, idx: int, v: V, ptr: str = "o"):
+    from .core import lit
+    em.line(f"{ptr}[{idx}] = {lit(v.c) if v.is_const else v.s};")
+
+
+class Body:
+    """Result of emitting one algorithm: C statements + number of per-thread state slots."""
+
+    def __init__(self, name: str, args: str, cx: Ctx, doc: str):
+        self.name, self.args, self.doc = name, args, doc
+        self.code = cx.em.code()
+        self.nslots = cx.em.nslots
+        self.n_ops = cx.em.n_ops
+
+
+def body_inverse_dynamics(model: Model, use_qdd: bool) -> Body:
+    cx = Ctx(model)
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_") if use_qdd else None
+    rnea_forward(cx, qd, qdd, keep=False)
+    c = rnea_backward(cx, qd, keep_f=False)
+    for j, v in enumerate(c):
+        _out(cx.em, j, v)
+    return Body("inverse_dynamics_inner", "", cx, "c = RNEA(q, qd, qdd)")
+
+
+def body_direct_minv(model: Model) -> Body:
+    cx = Ctx(model)
+    cx.prologue()
+    articulated_inertias(cx)
+    Minv = minv_columns(cx)
+    n = model.n
+    for col in range(n):
+        for r in range(n):
+            _out(cx.em, col * n + r, minv_get(Minv, r, col))
+    return Body("direct_minv_inner", "", cx, "Minv(q), dense symmetric, column-major")
+
+
+def body_forward_dynamics(model: Model) -> Body:
+    cx = Ctx(model)
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    u = cx.read_vec("u", "u_")
+    rnea_forward(cx, qd, None, keep=False)
+    c = rnea_backward(cx, qd, keep_f=False)
+    articulated_inertias(cx)
+    Minv = minv_columns(cx)
+    qdd = fd_finish(cx, Minv, u, c)
+    for j, v in enumerate(qdd):
+        _out(cx.em, j, v)
+    return Body("forward_dynamics_inner", "", cx, "qdd = Minv (u - RNEA(q, qd, 0))")
+
+
+def body_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> Body:
+    cx = Ctx(model)
+    n = model.n
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_") if use_qdd else None
+    rnea_forward(cx, qd, qdd, keep=True)
+    rnea_backward(cx, qd, keep_f=True)
+
+    def sink(c, dcq, dcd):
+        for r in range(n):
+            _out(cx.em, c * n + r, dcq[r])
+            _out(cx.em, (n + c) * n + r, dcd[r])
+
+    rnea_grad_columns(cx, qd, sink)
+    return Body("inverse_dynamics_gradient_inner", "", cx, "[dc/dq | dc/dqd], column-major n x 2n")
+
+
+def body_forward_dynamics_gradient(model: Model) -> Body:
+    cx = Ctx(model)
+    em, n = cx.em, model.n
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    u = cx.read_vec("u", "u_")
+    em.comment("---- pass 1: bias forces c = RNEA(q, qd, 0)")
+    rnea_forward(cx, qd, None, keep=False)
+    c = rnea_backward(cx, qd, keep_f=False)
+    em.comment("---- Minv")
+    articulated_inertias(cx)
+    Minv = minv_columns(cx)
+    qdd = fd_finish(cx, Minv, u, c)
+    store_minv(cx, Minv)
+    keys = list(Minv.keys())
+    em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
+    rnea_forward(cx, qd, qdd, keep=True)
+    rnea_backward(cx, qd, keep_f=True)
+    em.comment("---- grad RNEA columns and df_du = -Minv dc_du")
+
+    def sink(c_, dcq, dcd):
+        Mi = load_minv(cx, keys)
+        for r in range(n):
+            _out(em, c_ * n + r, em.lincomb([(-1.0, minv_get(Mi, r, k), dcq[k]) for k in range(n)]))
+            _out(em, (n + c_) * n + r, em.lincomb([(-1.0, minv_get(Mi, r, k), dcd[k]) for k in range(n)]))
+
+    rnea_grad_columns(cx, qd, sink)
+    return Body("forward_dynamics_gradient_inner", "", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]")
+
+
+def body_forward_dynamics_gradient_qdd_minv(model: Model) -> Body:
+    """grad FD when the caller already has qdd and Minv (reference USE_QDD_MINV_FLAG mode,
+    algorithms/_forward_dynamics_gradient.py:64-105): RNEA(q, qd, qdd) -> grad RNEA -> -Minv dc_du."""
+    cx = Ctx(model)
+    em, n = cx.em, model.n
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_")
+    rnea_forward(cx, qd, qdd, keep=True)
+    rnea_backward(cx, qd, keep_f=True)
+
+    def sink(c_, dcq, dcd):
+        Mi = [[em.tmp(f"Minv[{k * n + r}]") for k in range(n)] for r in range(n)]
+        for r in range(n):
+            _out(em, c_ * n + r, em.lincomb([(-1.0, Mi[r][k], dcq[k]) for k in range(n)]))
+            _out(em, (n + c_) * n + r, em.lincomb([(-1.0, Mi[r][k], dcd[k]) for k in range(n)]))
+
+    rnea_grad_columns(cx, qd, sink)
+    return Body("forward_dynamics_gradient_inner", "", cx, "-Minv [dc/dq | dc/dqd] with qdd and Minv supplied")

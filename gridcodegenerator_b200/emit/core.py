@@ -1,0 +1,212 @@
+"""Expression layer of the kernel emitter.
+
+The emitted kernels are straight-line, robot-specialised code: every quantity
+is either a compile-time constant (folded here, in Python) or a named scalar in
+the generated CUDA source.  Structural zeros / +-1 of the tree transforms and
+inertias therefore never reach the GPU, and the joint loop is fully unrolled
+with compile-time topology (the reference gets the same effect by printing
+robot-specific code: helpers/_topology_helpers.py:155-331, but keeps dense 6x6
+dot products at run time, helpers/_spatial_algebra_helpers.py:124-143).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+Number = Union[int, float]
+
+
+class V:
+    """A scalar: compile-time constant (`c`) or a C identifier/expression (`s`)."""
+
+    __slots__ = ("c", "s")
+
+    def __init__(self, c: Optional[float] = None, s: Optional[str] = None):
+        self.c = None if c is None else float(c)
+        self.s = s
+
+    @property
+    def is_const(self):
+        return self.c is not None
+
+    def is_zero(self):
+        return self.c is not None and self.c == 0.0
+
+    def __repr__(self):
+        return f"V({self.c if self.is_const else self.s})"
+
+
+ZERO = V(0.0)
+ONE = V(1.0)
+
+
+def const(x: Number) -> V:
+    return V(c=float(x))
+
+
+def lit(x: float) -> str:
+    """C literal usable for T = float or double."""
+    if x == int(x) and abs(x) < 1e6:
+        return f"T({int(x)})"
+    return f"T({x!r})"
+
+
+class Em:
+    """Code buffer + SSA temp allocator + per-thread state-slot allocator."""
+
+    def __init__(self, state_name: str = "S", stride_name: str = "NT"):
+        self.lines: List[str] = []
+        self.ctr = 0
+        self.state_name = state_name
+        self.stride_name = stride_name
+        self.slots: Dict[Tuple, int] = {}
+        self.free: List[int] = []
+        self.nslots = 0
+        self.const_slots: Dict[Tuple, float] = {}  # values known at emit time are never stored
+        self.n_ops = 0  # multiply/add operations emitted (for the executed-FLOP audit)
+
+    # ------------------------------------------------------------------ text
+    def line(self, txt: str):
+        self.lines.append(txt)
+
+    def comment(self, txt: str):
+        self.lines.append("// " + txt)
+
+    def tmp(self, expr: str) -> V:
+        name = f"t{self.ctr}"
+        self.ctr += 1
+        self.lines.append(f"const T {name} = {expr};")
+        return V(s=name)
+
+    def named(self, name: str, expr: str) -> V:
+        self.lines.append(f"const T {name} = {expr};")
+        return V(s=name)
+
+    def code(self, indent: str = "    ") -> str:
+        return "\n".join(indent + l for l in self.lines) + "\n"
+
+    # ------------------------------------------------------------ arithmetic
+    def lincomb(self, terms: Sequence[Tuple], acc: Optional[V] = None) -> V:
+        """sum_k coef_k * x_k [* y_k] (+ acc).  terms: (coef, x) or (coef, x, y) with coef a Python
+        float and x, y V's.  Constants are folded; emits at most one statement."""
+        csum = 0.0
+        parts: List[Tuple[float, str]] = []
+        if acc is not None:
+            if acc.is_const:
+                csum += acc.c
+            else:
+                parts.append((1.0, acc.s))
+        for t in terms:
+            coef = float(t[0])
+            vs = t[1:]
+            names = []
+            for v in vs:
+                if v is None:
+                    continue
+                if v.is_const:
+                    coef *= v.c
+                else:
+                    names.append(v.s)
+            if coef == 0.0:
+                continue
+            if not names:
+                csum += coef
+            else:
+                parts.append((coef, "*".join(names)))
+        if not parts:
+            return const(csum)
+        if len(parts) == 1 and csum == 0.0 and parts[0][0] == 1.0 and "*" not in parts[0][1]:
+            return V(s=parts[0][1])  # pure alias, no code
+        out = []
+        # put a positive term first so the expression does not start with a negation when avoidable
+        parts.sort(key=lambda p: p[0] < 0)
+        for i, (coef, name) in enumerate(parts):
+            mag = abs(coef)
+            body = name if mag == 1.0 else f"{lit(mag)}*{name}"
+            self.n_ops += name.count("*") + (0 if mag == 1.0 else 1) + (1 if i else 0)
+            if i == 0:
+                out.append(body if coef > 0 else f"-{body}")
+            else:
+                out.append((" + " if coef > 0 else " - ") + body)
+        if csum != 0.0:
+            out.append((" + " if csum > 0 else " - ") + lit(abs(csum)))
+            self.n_ops += 1
+        return self.tmp("".join(out))
+
+    def add(self, a: V, b: V) -> V:
+        return self.lincomb([(1.0, a), (1.0, b)])
+
+    def sub(self, a: V, b: V) -> V:
+        return self.lincomb([(1.0, a), (-1.0, b)])
+
+    def mul(self, a: V, b: V) -> V:
+        return self.lincomb([(1.0, a, b)])
+
+    def neg(self, a: V) -> V:
+        return self.lincomb([(-1.0, a)])
+
+    def recip(self, a: V) -> V:
+        if a.is_const:
+            return const(1.0 / a.c)
+        self.n_ops += 1
+        return self.tmp(f"T(1)/{a.s}")
+
+    def vadd(self, a: Sequence[V], b: Sequence[V]) -> List[V]:
+        return [self.add(x, y) for x, y in zip(a, b)]
+
+    def dot(self, a: Sequence[V], b: Sequence[V], acc: Optional[V] = None, sign: float = 1.0) -> V:
+        return self.lincomb([(sign, x, y) for x, y in zip(a, b)], acc)
+
+    def matvec(self, M: Sequence[Sequence[V]], x: Sequence[V], acc: Optional[Sequence[V]] = None) -> List[V]:
+        return [self.dot(M[r], x, None if acc is None else acc[r]) for r in range(len(M))]
+
+    def matTvec(self, M: Sequence[Sequence[V]], x: Sequence[V], acc: Optional[Sequence[V]] = None) -> List[V]:
+        rows, cols = len(M), len(M[0])
+        return [self.dot([M[r][c] for r in range(rows)], x, None if acc is None else acc[c]) for c in range(cols)]
+
+    # ------------------------------------------------------------ state slots
+    def slot(self, *key) -> int:
+        if key not in self.slots:
+            if self.free:
+                self.slots[key] = self.free.pop()
+            else:
+                self.slots[key] = self.nslots
+                self.nslots += 1
+        return self.slots[key]
+
+    def release(self, *key):
+        """Return a slot to the pool (its value is dead from here on)."""
+        idx = self.slots.pop(key, None)
+        if idx is not None:
+            self.free.append(idx)
+
+    def store(self, key: Tuple, v: V):
+        """Store v into the state slot `key`; constants are remembered at emit time, not stored."""
+        if v.is_const:
+            self.const_slots[key] = v.c
+            self.release(*key)
+            return
+        self.const_slots.pop(key, None)
+        idx = self.slot(*key)
+        self.lines.append(f"{self.state_name}[{idx}*{self.stride_name}] = {v.s};")
+
+    def load(self, key: Tuple) -> V:
+        if key in self.const_slots:
+            return const(self.const_slots[key])
+        idx = self.slots[key]
+        return self.tmp(f"{self.state_name}[{idx}*{self.stride_name}]")
+
+    def store_vec(self, name, j, vec: Sequence[V]):
+        for k, v in enumerate(vec):
+            self.store((name, j, k), v)
+
+    def load_vec(self, name, j, m: int = 6) -> List[V]:
+        return [self.load((name, j, k)) for k in range(m)]
+
+    def release_vec(self, name, j, m: int = 6):
+        for k in range(m):
+            self.release(name, j, k)
+
+
+def cmat(A) -> List[List[V]]:
+    """numpy matrix -> matrix of constant V's."""
+    return [[const(x) for x in row] for row in A]

@@ -1,0 +1,306 @@
+"""Text emitters for the four tiers of every algorithm in grid.cuh.
+
+Tier names are the reference's (README.md:25-30; banner GRiDCodeGenerator.py:312-380):
+  <algo>_inner   per-thread straight-line body (one lane = one knot point)
+  <algo>_device  per-warp tile loop (TMA staging + inner) callable from a user kernel
+  <algo>_kernel  __global__ with the reference's parameter list
+  <algo>         __host__ wrapper on gridData<T> (+ _single_timing, _compute_only)
+plus  <algo>_launch  the stream-asynchronous launcher the C ABI binds.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, List, Optional, Tuple
+
+from . import algos
+from .spatial import Model
+
+SMEM_LIMIT = 232448 - 1024   # 227 KB opt-in maximum per CTA minus the per-CTA reservation
+
+
+@dataclass
+class AlgoSpec:
+    key: str                 # python-side generator name, e.g. "forward_dynamics_gradient"
+    fn: str                  # C++ function stem
+    code: str                # shared-memory constant prefix (ID, MINV, FD, ID_DU, FD_DU, ...)
+    tag: str                 # unique suffix distinguishing overloads ("", "_qdd", ...)
+    body: Callable[[Model], algos.Body]
+    inner_inputs: List[str]  # pointer names of the inner function, in order
+    streams: List[Tuple[str, str]]  # (kernel parameter name, elements per knot as C expr of n)
+    split: List[Tuple[int, int]]    # inner input k comes from (stream index, element offset)
+    out_name: str
+    out_n: Callable[[int], int]
+    uses_gravity: bool = True
+    extra_kernel_params: str = ""
+
+
+def specs(n: int) -> List[AlgoSpec]:
+    return [
+        AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "", lambda m: algos.body_inverse_dynamics(m, False),
+                 ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_c", lambda n: n),
+        AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "_qdd", lambda m: algos.body_inverse_dynamics(m, True),
+                 ["q", "qd", "qdd"], [("d_q_qd", 2 * n), ("d_qdd", n)], [(0, 0), (0, n), (1, 0)], "d_c", lambda n: n),
+        AlgoSpec("direct_minv", "direct_minv", "MINV", "", algos.body_direct_minv,
+                 ["q"], [("d_q", n)], [(0, 0)], "d_Minv", lambda n: n * n, uses_gravity=False),
+        AlgoSpec("forward_dynamics", "forward_dynamics", "FD", "", algos.body_forward_dynamics,
+                 ["q", "qd", "u"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_qdd", lambda n: n),
+        AlgoSpec("inverse_dynamics_gradient", "inverse_dynamics_gradient", "ID_DU", "",
+                 lambda m: algos.body_inverse_dynamics_gradient(m, False),
+                 ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_dc_du", lambda n: 2 * n * n),
+        AlgoSpec("inverse_dynamics_gradient", "inverse_dynamics_gradient", "ID_DU", "_qdd",
+                 lambda m: algos.body_inverse_dynamics_gradient(m, True),
+                 ["q", "qd", "qdd"], [("d_q_qd", 2 * n), ("d_qdd", n)], [(0, 0), (0, n), (1, 0)], "d_dc_du",
+                 lambda n: 2 * n * n),
+        AlgoSpec("forward_dynamics_gradient", "forward_dynamics_gradient", "FD_DU", "",
+                 algos.body_forward_dynamics_gradient,
+                 ["q", "qd", "u"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_df_du", lambda n: 2 * n * n),
+        AlgoSpec("forward_dynamics_gradient", "forward_dynamics_gradient", "FD_DU", "_qdd_minv",
+                 algos.body_forward_dynamics_gradient_qdd_minv,
+                 ["q", "qd", "qdd", "Minv"], [("d_q_qd", 2 * n), ("d_qdd", n), ("d_Minv", n * n)],
+                 [(0, 0), (0, n), (1, 0), (2, 0)], "d_df_du", lambda n: 2 * n * n),
+    ]
+
+
+def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
+    """(NT, STATE_SMEM, STAGED) for one algorithm and scalar size.
+
+    Single-warp CTAs (NT = 32): warps never talk to each other, so the smallest CTA gives the finest
+    shared-memory packing (resident warps per SM = floor(227 KB / bytes per warp)) and the best tail."""
+    NT = 32
+    a16 = lambda x: (x + 15) & ~15
+    state = a16(slots * NT * sizeof)
+    stage = sum(2 * a16(32 * e * sizeof) for e in in_elems) + a16(32 * out_elems * sizeof) + 16
+    if state + stage + 16 <= SMEM_LIMIT:
+        return NT, True, True
+    if state + 16 <= SMEM_LIMIT:
+        return NT, True, False
+    return NT, False, False
+
+
+def algo_struct_name(sp: AlgoSpec) -> str:
+    return f"{sp.fn}{sp.tag}_algo"
+
+
+def emit_inner(sp: AlgoSpec, body: algos.Body) -> str:
+    ins = "".join(f"const T* __restrict__ {p}, " for p in sp.inner_inputs)
+    grav = "const T gravity" if sp.uses_gravity else "const T /*gravity*/"
+    doc = (f"/**\n * {body.doc}\n * One thread = one knot point. o: this knot's outputs; inputs: this knot's "
+           f"vectors;\n * S: this thread's state base (element i at S[i*NT], {body.nslots} elements).\n"
+           f" * Emitted operations (mul+add): {body.n_ops}\n */\n")
+    head = (f"template <typename T, int NT>\n__device__ __forceinline__\n"
+            f"void {sp.fn}_inner(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n")
+    return doc + head + "    using grid_rt::grid_sincos;\n" + body.code + "}\n\n"
+
+
+def emit_algo_struct(sp: AlgoSpec, body: algos.Body, n: int) -> str:
+    IN = [e for _, e in sp.streams] + [0, 0, 0]
+    args = []
+    for (s, off) in sp.split:
+        args.append(f"x{s}" + (f" + {off}" if off else ""))
+    call = f"{sp.fn}_inner<T, NT>(o, {', '.join(args)}, S, gravity);"
+    return (f"template <typename T>\nstruct {algo_struct_name(sp)} {{\n"
+            f"    static constexpr int IN0 = {IN[0]}, IN1 = {IN[1]}, IN2 = {IN[2]};\n"
+            f"    static constexpr int OUT = {sp.out_n(n)};\n"
+            f"    static constexpr int SLOTS = {max(body.nslots, 1)};\n"
+            f"    template <int NT>\n"
+            f"    static __device__ __forceinline__ void run(T* __restrict__ o, const T* __restrict__ x0, "
+            f"const T* __restrict__ x1, const T* __restrict__ x2, T* __restrict__ S, const T gravity) {{\n"
+            f"        {call}\n    }}\n}};\n\n")
+
+
+def emit_config(sp: AlgoSpec, body: algos.Body, n: int) -> str:
+    IN = [e for _, e in sp.streams]
+    out = sp.out_n(n)
+    c4 = choose_config(max(body.nslots, 1), IN, out, 4)
+    c8 = choose_config(max(body.nslots, 1), IN, out, 8)
+    b = lambda x: "true" if x else "false"
+    name = f"{sp.fn}{sp.tag}_cfg"
+    A = algo_struct_name(sp)
+    return (f"template <typename T>\nstruct {name} {{\n"
+            f"    static constexpr int NT = sizeof(T) == 4 ? {c4[0]} : {c8[0]};\n"
+            f"    static constexpr bool STATE_SMEM = sizeof(T) == 4 ? {b(c4[1])} : {b(c8[1])};\n"
+            f"    static constexpr bool STAGED = sizeof(T) == 4 ? {b(c4[2])} : {b(c8[2])};\n"
+            f"    static constexpr size_t SMEM_BYTES = grid_rt::tile_smem_bytes<{A}<T>, T, NT, STATE_SMEM, STAGED>();\n"
+            f"}};\n\n")
+
+
+def kernel_params(sp: AlgoSpec) -> str:
+    ps = [f"T *{sp.out_name}"]
+    first = True
+    for name, _ in sp.streams:
+        ps.append(f"const T *{name}")
+        if first:
+            ps.append(f"const int stride_{name[2:]}")
+            first = False
+    ps.append("const robotModel<T> *d_robotModel")
+    if sp.uses_gravity:
+        ps.append("const T gravity")
+    ps.append("const int NUM_TIMESTEPS")
+    return ", ".join(ps)
+
+
+def emit_device_and_kernel(sp: AlgoSpec, n: int) -> str:
+    A = algo_struct_name(sp)
+    C = f"{sp.fn}{sp.tag}_cfg<T>"
+    tl = f"grid_rt::tile_loop<{A}<T>, T, {C}::NT, {C}::STATE_SMEM, {C}::STAGED>"
+    fill = []
+    for i, (name, e) in enumerate(sp.streams):
+        stride = f"stride_{sp.streams[0][0][2:]}" if i == 0 else str(e)
+        fill.append(f"    a.in[{i}] = {name}; a.stride[{i}] = {stride};")
+    for i in range(len(sp.streams), 3):
+        fill.append(f"    a.in[{i}] = nullptr; a.stride[{i}] = 0;")
+    grav = "gravity" if sp.uses_gravity else "T(0)"
+    dev = (f"/** Per-warp tile loop of {sp.fn}: call from every thread of a kernel launched with\n"
+           f" *  {sp.code}_DYNAMIC_SHARED_MEM_COUNT*sizeof(T) bytes of dynamic shared memory. */\n"
+           f"template <typename T>\n__device__ __forceinline__\n"
+           f"void {sp.fn}_device(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) {{\n"
+           f"    {tl}(a, s_mem);\n}}\n\n") if sp.tag == "" else ""
+    # overloads of _device are distinguished by the algo struct, so tagged variants get a tagged name
+    if sp.tag:
+        dev = (f"template <typename T>\n__device__ __forceinline__\n"
+               f"void {sp.fn}{sp.tag}_device(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) {{\n"
+               f"    {tl}(a, s_mem);\n}}\n\n")
+    ker = (f"template <typename T>\n__global__ void __launch_bounds__({C}::NT, 1)\n"
+           f"{sp.fn}_kernel({kernel_params(sp)}) {{\n"
+           f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"
+           f"    grid_rt::TileArgs<T> a;\n" + "\n".join(fill) + "\n"
+           f"    a.out = {sp.out_name}; a.scratch = d_robotModel ? d_robotModel->d_scratch : nullptr;\n"
+           f"    a.gravity = {grav}; a.num_knots = NUM_TIMESTEPS;\n"
+           f"    {sp.fn}{sp.tag}_device<T>(a, grid_smem);\n}}\n\n")
+    return dev + ker
+
+
+def emit_launch(sp: AlgoSpec, n: int) -> str:
+    """Stream-asynchronous launcher: persistent grid sized from the occupancy of this kernel."""
+    C = f"{sp.fn}{sp.tag}_cfg<T>"
+    ps = [f"T *{sp.out_name}"]
+    call = [sp.out_name]
+    first = True
+    for name, _ in sp.streams:
+        ps.append(f"const T *{name}")
+        call.append(name)
+        if first:
+            ps.append(f"const int stride_{name[2:]}")
+            call.append(f"stride_{name[2:]}")
+            first = False
+    ps.append("const robotModel<T> *d_robotModel")
+    call.append("d_robotModel")
+    if sp.uses_gravity:
+        ps.append("const T gravity")
+        call.append("gravity")
+    ps.append("const int num_timesteps")
+    call.append("num_timesteps")
+    ps.append("cudaStream_t stream")
+    kfn = f"{sp.fn}_kernel<T>"
+    return (f"template <typename T>\n__host__\ncudaError_t {sp.fn}{sp.tag}_launch({', '.join(ps)}) {{\n"
+            f"    if (num_timesteps <= 0) return cudaSuccess;\n"
+            f"    auto kern = static_cast<void (*)({_sig_types(sp)})>({kfn});\n"
+            f"    int blocks = grid_rt::persistent_blocks(reinterpret_cast<const void*>(kern), {C}::NT, "
+            f"{C}::SMEM_BYTES, num_timesteps);\n"
+            f"    if (blocks <= 0) {{ cudaError_t e = cudaGetLastError(); return e != cudaSuccess ? e : cudaErrorLaunchOutOfResources; }}\n"
+            f"    if (!{C}::STATE_SMEM) {{\n"
+            f"        const int cap = grid_rt::scratch_blocks();\n"
+            f"        if (cap <= 0 || d_robotModel == nullptr) return cudaErrorInvalidValue;\n"
+            f"        if (blocks > cap) blocks = cap;\n"
+            f"    }}\n"
+            f"    kern<<<blocks, {C}::NT, {C}::SMEM_BYTES, stream>>>({', '.join(call)});\n"
+            f"    return cudaGetLastError();\n}}\n\n")
+
+
+def _sig_types(sp: AlgoSpec) -> str:
+    ts = ["T*"]
+    first = True
+    for _ in sp.streams:
+        ts.append("const T*")
+        if first:
+            ts.append("const int")
+            first = False
+    ts.append("const robotModel<T>*")
+    if sp.uses_gravity:
+        ts.append("const T")
+    ts.append("const int")
+    return ", ".join(ts)
+
+
+# ------------------------------------------------------------------ host tier
+@dataclass
+class HostSpec:
+    fn: str
+    tmpl: str                       # template parameter list after "typename T"
+    label: str                      # name printed by _single_timing
+    uses_gravity: bool
+    pre: List[str]                  # lines computing stride / pointers
+    h2d: List[Tuple[str, str, str, str]]   # (condition or "", d_ptr, h_ptr, elements per knot)
+    launch: List[str]               # lines performing the launch into `err`
+    d2h: Tuple[str, str, str]       # (d_ptr, h_ptr, elements per knot)
+
+
+def host_specs(n: int) -> List[HostSpec]:
+    comp = ["const int stride_q_qd = USE_COMPRESSED_MEM ? 2*NUM_JOINTS : 3*NUM_JOINTS;",
+            "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q_qd : hd_data->d_q_qd_u;",
+            "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q_qd : hd_data->h_q_qd_u;"]
+    return [
+        HostSpec("inverse_dynamics", ", bool USE_QDD_FLAG = false, bool USE_COMPRESSED_MEM = false", "ID", True, comp,
+                 [("", "d_in", "h_in", "stride_q_qd"), ("USE_QDD_FLAG", "hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS")],
+                 ["if (USE_QDD_FLAG) err = inverse_dynamics_qdd_launch<T>(hd_data->d_c, d_in, stride_q_qd, hd_data->d_qdd, d_robotModel, gravity, num_timesteps, 0);",
+                  "else err = inverse_dynamics_launch<T>(hd_data->d_c, d_in, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_c", "hd_data->h_c", "NUM_JOINTS")),
+        HostSpec("direct_minv", ", bool USE_COMPRESSED_MEM = false", "Minv", False,
+                 ["const int stride_q = USE_COMPRESSED_MEM ? NUM_JOINTS : 3*NUM_JOINTS;",
+                  "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q : hd_data->d_q_qd_u;",
+                  "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q : hd_data->h_q_qd_u;"],
+                 [("", "d_in", "h_in", "stride_q")],
+                 ["err = direct_minv_launch<T>(hd_data->d_Minv, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                 ("hd_data->d_Minv", "hd_data->h_Minv", "NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("forward_dynamics", "", "FD", True, ["const int stride_q_qd_u = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd_u")],
+                 ["err = forward_dynamics_launch<T>(hd_data->d_qdd, hd_data->d_q_qd_u, stride_q_qd_u, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS")),
+        HostSpec("inverse_dynamics_gradient", ", bool USE_QDD_FLAG = false, bool USE_COMPRESSED_MEM = false", "ID_DU",
+                 True, comp,
+                 [("", "d_in", "h_in", "stride_q_qd"), ("USE_QDD_FLAG", "hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS")],
+                 ["if (USE_QDD_FLAG) err = inverse_dynamics_gradient_qdd_launch<T>(hd_data->d_dc_du, d_in, stride_q_qd, hd_data->d_qdd, d_robotModel, gravity, num_timesteps, 0);",
+                  "else err = inverse_dynamics_gradient_launch<T>(hd_data->d_dc_du, d_in, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_dc_du", "hd_data->h_dc_du", "2*NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("forward_dynamics_gradient", ", bool USE_QDD_MINV_FLAG = false", "FD_DU", True,
+                 ["const int stride_q_qd = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd"),
+                  ("USE_QDD_MINV_FLAG", "hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS"),
+                  ("USE_QDD_MINV_FLAG", "hd_data->d_Minv", "hd_data->h_Minv", "NUM_JOINTS*NUM_JOINTS")],
+                 ["if (USE_QDD_MINV_FLAG) err = forward_dynamics_gradient_qdd_minv_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, hd_data->d_qdd, hd_data->d_Minv, d_robotModel, gravity, num_timesteps, 0);",
+                  "else err = forward_dynamics_gradient_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_df_du", "hd_data->h_df_du", "2*NUM_JOINTS*NUM_JOINTS")),
+    ]
+
+
+def emit_host(hs: HostSpec, mode: int) -> str:
+    """mode 0: H2D + kernel + D2H (blocking, like the reference); 1: _single_timing; 2: _compute_only.
+    block_dimms / thread_dimms are accepted for source compatibility; the persistent grid is sized by
+    occupancy (reference host tier: algorithms/_forward_dynamics_gradient.py:186-249)."""
+    suffix = {0: "", 1: "_single_timing", 2: "_compute_only"}[mode]
+    grav = "const T gravity, " if hs.uses_gravity else ""
+    streams = "" if mode == 2 else ", cudaStream_t *streams"
+    out = [f"template <typename T{hs.tmpl}>", "__host__",
+           f"void {hs.fn}{suffix}(gridData<T> *hd_data, const robotModel<T> *d_robotModel, {grav}const int num_timesteps,",
+           f"        const dim3 block_dimms, const dim3 thread_dimms{streams}) {{",
+           "    (void)block_dimms; (void)thread_dimms;", "    cudaError_t err = cudaSuccess;"]
+    out += ["    " + l for l in hs.pre]
+    if mode != 2:
+        for i, (cond, d, h, cnt) in enumerate(hs.h2d):
+            line = f"gpuErrchk(cudaMemcpyAsync({d}, {h}, size_t({cnt})*num_timesteps*sizeof(T), cudaMemcpyHostToDevice, streams[{i}]));"
+            out.append("    " + (f"if ({cond}) " if cond else "") + line)
+        out.append("    gpuErrchk(cudaDeviceSynchronize());")
+    if mode == 1:
+        out.append("    struct timespec start, end; clock_gettime(CLOCK_MONOTONIC, &start);")
+    out += ["    " + l for l in hs.launch]
+    out.append("    gpuErrchk(err);")
+    out.append("    gpuErrchk(cudaDeviceSynchronize());")
+    if mode == 1:
+        out.append("    clock_gettime(CLOCK_MONOTONIC, &end);")
+        out.append(f'    printf("Single Call {hs.label} %fus\\n", time_delta_us_timespec(start, end)/static_cast<double>(num_timesteps));')
+    if mode != 2:
+        d, h, cnt = hs.d2h
+        out.append(f"    gpuErrchk(cudaMemcpy({h}, {d}, size_t({cnt})*num_timesteps*sizeof(T), cudaMemcpyDeviceToHost));")
+        out.append("    gpuErrchk(cudaDeviceSynchronize());")
+    out.append("}")
+    return "\n".join(out) + "\n\n"

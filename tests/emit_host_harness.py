@@ -1,0 +1,56 @@
+"""Test helper: compile the EMITTED per-thread bodies (<algo>_inner) as plain host C++ (T = double,
+NT = 1) so the emitter's algebra can be checked against the golden vectors without a GPU.
+Not a product path: the product only ever runs these bodies inside the sm_100a tile kernels."""
+import ctypes
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+from gridcodegenerator_b200.GRiDCodeGenerator import GRiDCodeGenerator
+from gridcodegenerator_b200.emit import header as hdr
+
+PRELUDE = """
+#include <math.h>
+#include <stddef.h>
+#define __device__
+#define __forceinline__ inline
+#define __restrict__
+namespace grid_rt { static inline void grid_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); } }
+"""
+
+
+def build_host_inners(robot, workdir=None):
+    g = GRiDCodeGenerator(robot)
+    n = g.model.n
+    src = [PRELUDE]
+    wrappers = []
+    for name, sp in g._specs.items():
+        body = g._body(name)
+        src.append(hdr.emit_inner(sp, body))
+        ins = ", ".join(f"const double* {p}" for p in sp.inner_inputs)
+        call = ", ".join(sp.inner_inputs)
+        wrappers.append(
+            f'extern "C" void host_{name}(double* o, {ins}, double gravity) {{\n'
+            f"    static thread_local double S[{max(body.nslots, 1)}];\n"
+            f"    {sp.fn}_inner<double, 1>(o, {call}, S, gravity);\n}}\n")
+    text = "\n".join(src) + "\n".join(wrappers)
+    workdir = workdir or tempfile.mkdtemp(prefix="grid_host_")
+    cpp = os.path.join(workdir, f"inner_{robot.name}.cpp")
+    so = os.path.join(workdir, f"inner_{robot.name}.so")
+    with open(cpp, "w") as f:
+        f.write(text)
+    subprocess.check_call(["g++", "-O1", "-shared", "-fPIC", "-o", so, cpp])
+    lib = ctypes.CDLL(so)
+    return lib, g
+
+
+def call(lib, g, name, out_n, *inputs, gravity=9.81):
+    dp = ctypes.POINTER(ctypes.c_double)
+    out = np.zeros(out_n)
+    arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in inputs]
+    fn = getattr(lib, "host_" + name)
+    fn.restype = None
+    fn(out.ctypes.data_as(dp), *[a.ctypes.data_as(dp) for a in arrs], ctypes.c_double(gravity))
+    return out
