@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""Headline benchmark: grad-FD knot-points/sec, KUKA iiwa14, batch 65536 per GPU (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path (forward_dynamics_gradient, reference
+algorithms/_forward_dynamics_gradient.py:113-249) over one batch of 65536 synthetic knot points
+[q|qd|u] ~ U(-1,1).  Every rank owns its own batch (weak scaling, no collective on
+the data path); `value` is whole-job knots/s with the inputs resident in HBM, timed with CUDA events
+on the launching stream, max over ranks.  Between timed steps the kernel is pointed at the next of
+several input/output buffer sets whose total size exceeds the 126 MB L2, so no step re-reads its
+inputs from cache.  `e2e` is the same metric through the C-ABI host entry point
+(grid_forward_dynamics_gradient_host_f32: pinned host buffers, H2D and D2H inside the timed region).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ROBOT = "iiwa14"
+BATCH = 65536
+GRAVITY = 9.81
+# algorithmic work per knot point for iiwa14 grad FD
+N_JOINTS = 7
+BYTES_PER_KNOT = 4 * (3 * N_JOINTS + 2 * N_JOINTS * N_JOINTS)   # 476 B (fp32 in + out)
+MODEL_FLOPS_PER_KNOT = 44512                                    # dense 6x6 operation count of _test.py
+L2_BYTES = 126 * 1024 * 1024
+METRIC = "grad-FD knot-points/sec (iiwa14, batch 65536 per GPU)"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Polls SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.005):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period_s
+        self.samples, self.reasons = [], set()
+        self.active = threading.Event()
+        self.stop_flag = threading.Event()
+        self.max_mhz = None
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    NAMES = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+             0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            if self.active.is_set():
+                try:
+                    self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                    try:
+                        r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                    except Exception:
+                        r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                    for bit, name in self.NAMES.items():
+                        if r & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(self.period)
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def _dist():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def cpu_reference_leg(seconds: float, batch: int = BATCH):
+    """The reference's CPU algorithm for the path (oracle/rbd_oracle.c, a C restatement of reference
+    _test.py:496-520 pinned to its golden vectors), all host threads, whole batches until `seconds` pass."""
+    import numpy as np
+    from gridcodegenerator_b200.robot import load_robot
+    from oracle import Oracle
+    orc = Oracle(load_robot(ROBOT))
+    cores = Oracle.max_threads()
+    x = np.random.default_rng(0).uniform(-1, 1, (batch, 3 * N_JOINTS)).astype(np.float32).astype(np.float64)
+    orc.batch_fd_grad(x[:4096], nthreads=cores)  # warm
+    t0 = time.perf_counter()
+    done = 0
+    while True:
+        orc.batch_fd_grad(x, nthreads=cores)
+        done += batch
+        dt = time.perf_counter() - t0
+        if dt >= seconds:
+            break
+    return done / dt, cores, done, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores.
+    The reference itself is pure Python + NumPy and cannot travel to the GPU box (no /root/reference
+    there), so the timed code is the C port of it (cpu_baseline.kind = "port"); each step is one
+    bounded sample of the workload (8192 knots) on all host threads."""
+    rank, world, _ = _dist()
+    if rank != 0:
+        return 0
+    import numpy as np
+    from gridcodegenerator_b200.robot import load_robot
+    from oracle import Oracle
+    orc = Oracle(load_robot(ROBOT))
+    cores = Oracle.max_threads()
+    sample = 8192
+    x = np.random.default_rng(0).uniform(-1, 1, (sample, 3 * N_JOINTS)).astype(np.float32).astype(np.float64)
+    for _ in range(max(args.warmup, 1)):
+        orc.batch_fd_grad(x, nthreads=cores)
+    steps = max(1, min(args.steps, 200))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        orc.batch_fd_grad(x, nthreads=cores)
+    dt = time.perf_counter() - t0
+    value = sample * steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "knots/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "iiwa14 grad-FD, batch 65536 per GPU", "robot": ROBOT, "batch_per_gpu": BATCH,
+                   "sample_per_step": sample},
+        "cpu_baseline": {"value": value, "unit": "knots/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} steps x {sample} knots of the same seeded workload, C port of "
+                                   f"reference _test.py test_fd_grad, {cores} threads"},
+        "e2e": {"value": value, "unit": "knots/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local = _dist()
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from gridcodegenerator_b200.runtime import get_library
+    lib = get_library(ROBOT)
+    n = lib.n
+    assert n == N_JOINTS
+
+    # rotating buffer sets: total footprint > L2 so that no step finds its inputs in cache
+    set_bytes = BATCH * BYTES_PER_KNOT
+    nsets = max(2, -(-2 * L2_BYTES // set_bytes))
+    rng = np.random.default_rng(1000 + rank)
+    ins, outs = [], []
+    for s in range(nsets):
+        x = rng.uniform(-1, 1, (BATCH, 3 * n)).astype(np.float32)
+        ins.append(torch.from_numpy(x).cuda())
+        outs.append(torch.empty((BATCH, 2 * n * n), dtype=torch.float32, device="cuda"))
+    stream = torch.cuda.current_stream()
+
+    def step(i):
+        lib.forward_dynamics_gradient(ins[i % nsets], GRAVITY, out=outs[i % nsets])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active.set()
+    ev0.record(stream)
+    for i in range(args.steps):
+        step(i)
+    ev1.record(stream)
+    barrier()
+    sampler.active.clear()
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * BATCH * args.steps / (ms_max * 1e-3)
+    kernel_ms = ms / args.steps                         # one launch per step, back to back on one stream
+
+    # ---- end to end through the C-ABI host entry point (pinned host buffers)
+    h_in = torch.from_numpy(rng.uniform(-1, 1, (BATCH, 3 * n)).astype(np.float32)).pin_memory()
+    h_out = torch.empty((BATCH, 2 * n * n), dtype=torch.float32).pin_memory()
+    e2e_steps = max(3, min(args.steps, 50))
+    for _ in range(3):
+        lib.forward_dynamics_gradient_host(h_in, h_out, GRAVITY)
+    barrier()
+    sampler.active.set()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        lib.forward_dynamics_gradient_host(h_in, h_out, GRAVITY)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    sampler.active.clear()
+    sampler.stop_flag.set()
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * BATCH * e2e_steps / float(t.item())
+    checksum = float(h_out[:: 4096].double().abs().sum())
+
+    if rank == 0:
+        hbm_peak, sm_max_mhz, which = _peaks()
+        achieved_gbs = BYTES_PER_KNOT * BATCH / (kernel_ms * 1e-3) / 1e9
+        clocks = sampler.summary()
+        fp32_peak = 148 * 128 * 2 * (clocks.get("sm_max_mhz") or sm_max_mhz) * 1e6 / 1e12
+        model_tflops = MODEL_FLOPS_PER_KNOT * BATCH / (kernel_ms * 1e-3) / 1e12
+        cpu_v, cores, done, cpu_dt = cpu_reference_leg(args.cpu_seconds)
+        info = lib.kernel_info("forward_dynamics_gradient")
+        line = {
+            "metric": METRIC, "value": value, "unit": "knots/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "iiwa14 grad-FD, batch 65536 per GPU", "robot": ROBOT, "batch_per_gpu": BATCH,
+                       "gravity": GRAVITY, "parallelism": f"batch-sharded x{world}, no collective",
+                       "l2": f"rotating {nsets} input/output buffer sets ({nsets * set_bytes >> 20} MB > 126 MB L2)",
+                       "kernel": info, "persistent_blocks": lib.persistent_blocks("forward_dynamics_gradient")},
+            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": which,
+                         "kernel": "forward_dynamics_gradient_kernel<float>", "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_knot": BYTES_PER_KNOT,
+                         "fp32": {"model_flops_per_knot": MODEL_FLOPS_PER_KNOT, "achieved_tflops": model_tflops,
+                                  "peak_tflops": fp32_peak, "frac": model_tflops / fp32_peak,
+                                  "note": "path is FP32-pipe-bound (SURVEY 8(d)); model FLOPs = dense 6x6 count of "
+                                          "the reference algorithm, peak = 148 SM x 128 lanes x 2 x max SM clock"}},
+            "cpu_baseline": {"value": cpu_v, "unit": "knots/s", "cores": cores, "kind": "port",
+                             "sample": f"{done} knots of the same workload in {cpu_dt:.1f} s, C port of reference "
+                                       f"_test.py test_fd_grad (oracle/rbd_oracle.c), {cores} threads"},
+            "e2e": {"value": e2e_value, "unit": "knots/s", "h2d_bytes_per_step": BATCH * 3 * n * 4,
+                    "d2h_bytes_per_step": BATCH * 2 * n * n * 4, "steps": e2e_steps,
+                    "api": "grid_forward_dynamics_gradient_host_f32 (pinned host buffers, chunked 3-stream pipeline)",
+                    "checksum": checksum},
+            "gpu_launches": args.steps,
+            "clocks": clocks,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=4.0, help="wall time of the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

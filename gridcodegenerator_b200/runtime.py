@@ -1,0 +1,269 @@
+"""Build + load the per-robot C-ABI library and call it on torch device tensors.
+
+Python host side of the drop-in boundary (include/grid_b200.h).  torch is used only for device memory
+and streams; all arithmetic happens in the emitted sm_100a kernels.  There is NO CPU or eager fallback:
+if the library cannot be built/loaded or no CUDA device is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import hashlib
+import os
+import shutil
+import subprocess
+from typing import Optional
+
+from .GRiDCodeGenerator import GRiDCodeGenerator
+from .robot import load_robot
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG)
+BUILD_DIR = os.path.join(_PKG, "_build")
+CSRC = os.path.join(_PKG, "csrc")
+INCLUDE = os.path.join(_ROOT, "include")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-shared"]
+
+ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
+              "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
+              "forward_dynamics_gradient_qdd_minv": 7}
+
+
+def _nvcc() -> str:
+    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found: the GRiD B200 library cannot be built")
+
+
+def _source_digest(header_text: str) -> str:
+    h = hashlib.sha256()
+    h.update(header_text.encode())
+    for fn in ("grid_capi.cu",):
+        with open(os.path.join(CSRC, fn), "rb") as f:
+            h.update(f.read())
+    with open(os.path.join(INCLUDE, "grid_b200.h"), "rb") as f:
+        h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()[:16]
+
+
+def library_path(robot_name: str) -> str:
+    return os.path.join(BUILD_DIR, robot_name, f"libgrid_{robot_name}.so")
+
+
+def build_library(robot, force: bool = False, verbose: bool = False) -> str:
+    """Emit grid.cuh for `robot` (a robot object or the name of a shipped robot) and compile the C-ABI
+    library for sm_100a.  Returns the .so path.  Up-to-date builds are reused (digest of all sources)."""
+    if isinstance(robot, str):
+        robot = load_robot(robot)
+    name = robot.name
+    out_dir = os.path.join(BUILD_DIR, name)
+    os.makedirs(out_dir, exist_ok=True)
+    gen = GRiDCodeGenerator(robot)
+    gen.gen_all_code(output_dir=out_dir)
+    digest = _source_digest(gen.code_str)
+    so = library_path(name)
+    stamp = os.path.join(out_dir, "digest.txt")
+    if not force and os.path.exists(so) and os.path.exists(stamp) and open(stamp).read().strip() == digest:
+        return so
+    cmd = [_nvcc()] + NVCC_FLAGS + [f"-I{out_dir}", f"-I{INCLUDE}", f'-DGRID_ROBOT_NAME="{name}"',
+                                    os.path.join(CSRC, "grid_capi.cu"), "-o", so]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for robot {name}:\n{res.stdout[-4000:]}")
+    if verbose:
+        with open(os.path.join(out_dir, "ptxas.log"), "w") as f:
+            f.write(res.stdout)
+    with open(stamp, "w") as f:
+        f.write(digest)
+    return so
+
+
+_f32p = ctypes.c_void_p
+
+
+class GRiDLibrary:
+    """ctypes binding of libgrid_<robot>.so.  Tensors in, tensors out; asynchronous on the current torch stream."""
+
+    def __init__(self, robot, build: bool = True):
+        name = robot if isinstance(robot, str) else robot.name
+        so = library_path(name)
+        if not os.path.exists(so):
+            if not build:
+                raise RuntimeError(f"{so} is missing and build=False: no fallback path exists")
+            so = build_library(robot)
+        self.path = so
+        self.lib = ctypes.CDLL(so)
+        L = self.lib
+        L.grid_robot_name.restype = ctypes.c_char_p
+        L.grid_last_error.restype = ctypes.c_char_p
+        L.grid_kernel_info.restype = ctypes.c_long
+        L.grid_kernel_info.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        self.n = int(L.grid_num_joints())
+        self.name = L.grid_robot_name().decode()
+        vp, ci = ctypes.c_void_p, ctypes.c_int
+        for suf, g in (("f32", ctypes.c_float), ("f64", ctypes.c_double)):
+            getattr(L, f"grid_inverse_dynamics_{suf}").argtypes = [vp, ci, vp, vp, ci, g, vp]
+            getattr(L, f"grid_direct_minv_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_forward_dynamics_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_inverse_dynamics_gradient_{suf}").argtypes = [vp, ci, vp, vp, ci, g, vp]
+            getattr(L, f"grid_forward_dynamics_gradient_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_forward_dynamics_gradient_qdd_minv_{suf}").argtypes = [vp, ci, vp, vp, vp, ci, g, vp]
+            getattr(L, f"grid_forward_dynamics_gradient_host_{suf}").argtypes = [vp, vp, ci, g]
+        L.grid_forward_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
+        L.grid_inverse_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
+
+    # ------------------------------------------------------------------ helpers
+    def _check(self, rc: int):
+        if rc != 0:
+            raise RuntimeError(f"GRiD library error {rc}: {self.lib.grid_last_error().decode()}")
+
+    @staticmethod
+    def _suf(t) -> str:
+        import torch
+        if t.dtype == torch.float32:
+            return "f32"
+        if t.dtype == torch.float64:
+            return "f64"
+        raise TypeError(f"unsupported dtype {t.dtype}")
+
+    @staticmethod
+    def _dev(t, cols_min: int):
+        if not t.is_cuda:
+            raise RuntimeError("device entry points need CUDA tensors (no CPU fallback exists)")
+        if t.dim() != 2 or t.stride(1) != 1 or t.shape[1] < cols_min:
+            raise ValueError(f"expected a (B, >={cols_min}) row-major tensor, got {tuple(t.shape)} strides {t.stride()}")
+        return t.data_ptr(), int(t.stride(0)), int(t.shape[0])
+
+    @staticmethod
+    def _stream():
+        import torch
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def kernel_info(self, algo: str, f64: bool = False) -> dict:
+        i = ALGO_INDEX[algo]
+        keys = ("smem_bytes", "threads", "state_slots", "state_in_smem", "staged_io")
+        return {k: int(self.lib.grid_kernel_info(i, int(f64), w)) for w, k in enumerate(keys)}
+
+    def persistent_blocks(self, algo: str, f64: bool = False) -> int:
+        return int(self.lib.grid_kernel_info(ALGO_INDEX[algo], int(f64), 5))
+
+    # ------------------------------------------------------- device entry points
+    def inverse_dynamics(self, q_qd, qdd=None, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd, 2 * n)
+        suf = self._suf(q_qd)
+        out = torch.empty((B, n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        pq = None
+        if qdd is not None:
+            pq, sq, Bq = self._dev(qdd, n)
+            if sq != n or Bq != B:
+                raise ValueError("qdd must be a dense (B, n) tensor")
+        with torch.cuda.device(q_qd.device):
+            self._check(getattr(self.lib, f"grid_inverse_dynamics_{suf}")(p, stride, pq, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def direct_minv(self, q, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q, n)
+        suf = self._suf(q)
+        out = torch.empty((B, n * n), dtype=q.dtype, device=q.device) if out is None else out
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_direct_minv_{suf}")(p, stride, out.data_ptr(), B, self._stream()))
+        return out
+
+    def forward_dynamics(self, q_qd_u, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd_u, 3 * n)
+        suf = self._suf(q_qd_u)
+        out = torch.empty((B, n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        with torch.cuda.device(q_qd_u.device):
+            self._check(getattr(self.lib, f"grid_forward_dynamics_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def inverse_dynamics_gradient(self, q_qd, qdd=None, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd, 2 * n)
+        suf = self._suf(q_qd)
+        out = torch.empty((B, 2 * n * n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        pq = None
+        if qdd is not None:
+            pq, sq, Bq = self._dev(qdd, n)
+            if sq != n or Bq != B:
+                raise ValueError("qdd must be a dense (B, n) tensor")
+        with torch.cuda.device(q_qd.device):
+            self._check(getattr(self.lib, f"grid_inverse_dynamics_gradient_{suf}")(p, stride, pq, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def forward_dynamics_gradient(self, q_qd_u, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd_u, 3 * n)
+        suf = self._suf(q_qd_u)
+        out = torch.empty((B, 2 * n * n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        with torch.cuda.device(q_qd_u.device):
+            self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def forward_dynamics_gradient_qdd_minv(self, q_qd, qdd, Minv, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd, 2 * n)
+        suf = self._suf(q_qd)
+        pq, sq, _ = self._dev(qdd, n)
+        pm, sm, _ = self._dev(Minv, n * n)
+        if sq != n or sm != n * n:
+            raise ValueError("qdd and Minv must be dense")
+        out = torch.empty((B, 2 * n * n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        with torch.cuda.device(q_qd.device):
+            self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_qdd_minv_{suf}")(
+                p, stride, pq, pm, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    # --------------------------------------------------------- host entry points
+    def forward_dynamics_gradient_host(self, h_q_qd_u, h_out=None, gravity: float = 9.81):
+        """Host tensors in / out (pinned for full PCIe speed); H2D, kernel and D2H run inside the call."""
+        import torch
+        n = self.n
+        if h_q_qd_u.is_cuda or not h_q_qd_u.is_contiguous() or h_q_qd_u.shape[1] != 3 * n:
+            raise ValueError("expected a contiguous host (B, 3n) tensor")
+        B = h_q_qd_u.shape[0]
+        suf = self._suf(h_q_qd_u)
+        if h_out is None:
+            h_out = torch.empty((B, 2 * n * n), dtype=h_q_qd_u.dtype, pin_memory=True)
+        self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_host_{suf}")(h_q_qd_u.data_ptr(), h_out.data_ptr(), B, gravity))
+        return h_out
+
+    def forward_dynamics_host(self, h_q_qd_u, h_out=None, gravity: float = 9.81):
+        import torch
+        B = h_q_qd_u.shape[0]
+        if h_out is None:
+            h_out = torch.empty((B, self.n), dtype=torch.float32, pin_memory=True)
+        self._check(self.lib.grid_forward_dynamics_host_f32(h_q_qd_u.data_ptr(), h_out.data_ptr(), B, gravity))
+        return h_out
+
+    def inverse_dynamics_host(self, h_q_qd_qdd, h_out=None, gravity: float = 9.81):
+        import torch
+        B = h_q_qd_qdd.shape[0]
+        if h_out is None:
+            h_out = torch.empty((B, self.n), dtype=torch.float32, pin_memory=True)
+        self._check(self.lib.grid_inverse_dynamics_host_f32(h_q_qd_qdd.data_ptr(), h_out.data_ptr(), B, gravity))
+        return h_out
+
+
+_LIBS = {}
+
+
+def get_library(robot_name: str) -> GRiDLibrary:
+    if robot_name not in _LIBS:
+        _LIBS[robot_name] = GRiDLibrary(robot_name)
+    return _LIBS[robot_name]

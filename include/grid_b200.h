@@ -1,0 +1,95 @@
+/*
+ * grid_b200.h -- C ABI of one robot-specialised GRiD library (libgrid_<robot>.so).
+ *
+ * One shared library per robot, like the reference's one grid.cuh per robot
+ * (reference README.md:10-15, GRiDCodeGenerator.py:434-437).  Each entry point replaces the host tier
+ * of one algorithm of the reference's emitted header; the reference function it stands in for is cited
+ * per declaration (files relative to /root/reference).
+ *
+ * Conventions
+ *   - all matrices column-major, batches knot-major (reference helpers/_code_generation_helpers.py:57-61,
+ *     :147-164): knot k's inputs start at in + k*stride.
+ *   - `d_*` pointers are device memory owned by the caller; calls are asynchronous on `stream`
+ *     (a cudaStream_t passed as void*; NULL = default stream) and never allocate after the first call
+ *     for a robot/dtype on a device.  `h_*` entry points take host buffers (pinned or pageable), run
+ *     H2D -> kernel -> D2H internally and return when the result is in h_out.
+ *   - every function returns 0 on success or a cudaError_t value; grid_last_error() describes it.
+ *     Nothing calls exit() (the reference's gpuErrchk does: GRiDCodeGenerator.py:279-286).
+ *   - the current CUDA device of the calling thread is used.
+ *   - gravity is the positive magnitude (9.81), as in the reference kernels
+ *     (algorithms/_inverse_dynamics.py:123) == GRAVITY = -9.81 of _test.py:13-14.
+ */
+#ifndef GRID_B200_H
+#define GRID_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- introspection (reference constants NUM_JOINTS etc., GRiDCodeGenerator.py:86-111) ---- */
+int grid_num_joints(void);
+const char *grid_robot_name(void);
+const char *grid_last_error(void);
+int grid_abi_version(void);
+/* shared-memory bytes per CTA, threads per CTA, per-thread state elements of an algorithm's kernel
+ * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv); is_f64: 0/1
+ * what: 0 smem bytes, 1 threads, 2 state slots, 3 state in shared memory (0/1), 4 TMA-staged I/O (0/1),
+ *       5 persistent grid size for num_knots = 1<<20 on the current device */
+long grid_kernel_info(int algo, int is_f64, int what);
+
+/* ---- inverse dynamics c = RNEA(q, qd[, qdd])
+ * replaces inverse_dynamics<T,USE_QDD_FLAG,USE_COMPRESSED_MEM> (algorithms/_inverse_dynamics.py:440-512)
+ * d_q_qd: [q|qd] per knot, `stride` elements apart (2n compressed, 3n for a q_qd_u buffer);
+ * d_qdd: n per knot, dense, or NULL for qdd = 0; d_c: n per knot. */
+int grid_inverse_dynamics_f32(const float *d_q_qd, int stride, const float *d_qdd, float *d_c, int num_knots,
+                              float gravity, void *stream);
+int grid_inverse_dynamics_f64(const double *d_q_qd, int stride, const double *d_qdd, double *d_c, int num_knots,
+                              double gravity, void *stream);
+
+/* ---- direct inverse mass matrix, dense symmetric n x n per knot
+ * replaces direct_minv<T,USE_COMPRESSED_MEM> (algorithms/_direct_minv.py:527-588) */
+int grid_direct_minv_f32(const float *d_q, int stride, float *d_Minv, int num_knots, void *stream);
+int grid_direct_minv_f64(const double *d_q, int stride, double *d_Minv, int num_knots, void *stream);
+
+/* ---- forward dynamics qdd = Minv (u - c)
+ * replaces forward_dynamics<T> (algorithms/_forward_dynamics.py:199-260); d_q_qd_u: [q|qd|u] */
+int grid_forward_dynamics_f32(const float *d_q_qd_u, int stride, float *d_qdd, int num_knots, float gravity,
+                              void *stream);
+int grid_forward_dynamics_f64(const double *d_q_qd_u, int stride, double *d_qdd, int num_knots, double gravity,
+                              void *stream);
+
+/* ---- gradient of inverse dynamics [dc/dq | dc/dqd], n x 2n per knot
+ * replaces inverse_dynamics_gradient<T,USE_QDD_FLAG,USE_COMPRESSED_MEM>
+ * (algorithms/_inverse_dynamics_gradient.py:890-960) */
+int grid_inverse_dynamics_gradient_f32(const float *d_q_qd, int stride, const float *d_qdd, float *d_dc_du,
+                                       int num_knots, float gravity, void *stream);
+int grid_inverse_dynamics_gradient_f64(const double *d_q_qd, int stride, const double *d_qdd, double *d_dc_du,
+                                       int num_knots, double gravity, void *stream);
+
+/* ---- gradient of forward dynamics [dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd], n x 2n per knot
+ * replaces forward_dynamics_gradient<T,false> (algorithms/_forward_dynamics_gradient.py:186-249) */
+int grid_forward_dynamics_gradient_f32(const float *d_q_qd_u, int stride, float *d_df_du, int num_knots,
+                                       float gravity, void *stream);
+int grid_forward_dynamics_gradient_f64(const double *d_q_qd_u, int stride, double *d_df_du, int num_knots,
+                                       double gravity, void *stream);
+/* replaces forward_dynamics_gradient<T,true> (qdd and Minv supplied; same file :64-105, :223-228) */
+int grid_forward_dynamics_gradient_qdd_minv_f32(const float *d_q_qd, int stride, const float *d_qdd,
+                                                const float *d_Minv, float *d_df_du, int num_knots,
+                                                float gravity, void *stream);
+int grid_forward_dynamics_gradient_qdd_minv_f64(const double *d_q_qd, int stride, const double *d_qdd,
+                                                const double *d_Minv, double *d_df_du, int num_knots,
+                                                double gravity, void *stream);
+
+/* ---- host-buffer entry points (the reference's default host semantics: H2D, kernel, D2H, blocking;
+ * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / n out). */
+int grid_forward_dynamics_gradient_host_f32(const float *h_q_qd_u, float *h_df_du, int num_knots, float gravity);
+int grid_forward_dynamics_gradient_host_f64(const double *h_q_qd_u, double *h_df_du, int num_knots, double gravity);
+int grid_forward_dynamics_host_f32(const float *h_q_qd_u, float *h_qdd, int num_knots, float gravity);
+int grid_inverse_dynamics_host_f32(const float *h_q_qd_u, float *h_c, int num_knots, float gravity);
+/* release the cached device workspace of the host entry points and the robot model handles */
+int grid_release(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRID_B200_H */
