@@ -215,7 +215,7 @@ def gen_add_constants_helpers(self):
     per4, per8 = _scratch_constants(self)
     lines += [f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F64 = {per8};",
-              "const int GRID_SCRATCH_BLOCKS_PER_SM = 8;"]
+              "const int GRID_SCRATCH_BLOCKS_PER_SM = 2;"]
     self.gen_add_code_lines(lines)
     self._add_block(_sc.STRUCTS)
 

@@ -14,16 +14,35 @@ registers.  The algorithms follow the reference's CPU oracle:
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence
 
 from .core import Em, V, ZERO, ONE, const
 from .spatial import Model, Trig, Xform, fxv, inertia_mul, mxS, unit
 
 
+def fence_policy(n: int) -> bool:
+    """Fences at joint / column boundaries for robots whose live state would not fit the register file."""
+    mode = os.environ.get("GRID_EMIT_FENCES", "auto")
+    if mode in ("0", "1"):
+        return mode == "1"
+    return n > 8
+
+
+def regs_only_policy(n: int) -> bool:
+    """Robots small enough that the whole per-knot state fits registers + a little local memory."""
+    mode = os.environ.get("GRID_EMIT_REGS_ONLY", "auto")
+    if mode in ("0", "1"):
+        return mode == "1"
+    return n <= 8
+
+
 class Ctx:
     def __init__(self, model: Model, em: Optional[Em] = None):
         self.m = model
         self.em = em or Em()
+        self.em.fences = fence_policy(model.n)
+        self.em.regs_only = regs_only_policy(model.n)
         self.n = model.n
         self.X: List[Xform] = []
         self.q: List[V] = []
@@ -314,6 +333,8 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
         for j in sub:
             jd = m.joints[j]
             S = jd.S
+            if j != c:
+                em.comment(f"grad RNEA column {c}, forward joint {j}")
             v = em.load_vec("v", j)
             Iv = em.load_vec("Iv", j)
             if j == c:
@@ -341,6 +362,7 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
         dcq: List[V] = [ZERO] * n
         dcd: List[V] = [ZERO] * n
         rel = sorted(set(sub) | set(m.ancestors[c]), reverse=True)
+        em.comment(f"grad RNEA column {c}, backward sweep")
         for j in rel:
             jd = m.joints[j]
             fq, fd_ = ps_q.pull(j), ps_d.pull(j)

@@ -63,13 +63,25 @@ class Em:
         self.nslots = 0
         self.const_slots: Dict[Tuple, float] = {}  # values known at emit time are never stored
         self.n_ops = 0  # multiply/add operations emitted (for the executed-FLOP audit)
+        self.fences = False
+        # small robots: "state" is plain SSA values (registers; ptxas spills the coldest to local memory = L1)
+        self.regs_only = False
+        self.reg_state: Dict[Tuple, V] = {}
 
     # ------------------------------------------------------------------ text
     def line(self, txt: str):
         self.lines.append(txt)
 
     def comment(self, txt: str):
+        """Section marker.  With `fences` on, also a compiler-level memory fence: values loaded from the
+        state before the marker are not kept live in registers across it (they are re-read from shared
+        memory when needed), which bounds register pressure for big robots (Atlas: 38 KB of spills without)."""
         self.lines.append("// " + txt)
+        if self.fences:
+            self.lines.append("GRID_FENCE();")
+        # lockstep point: the warps of a CTA re-converge here so that they stream the (straight-line, >100 KB)
+        # code through the instruction caches together; a no-op for single-warp CTAs
+        self.lines.append("GRID_SYNC();")
 
     def tmp(self, expr: str) -> V:
         name = f"t{self.ctr}"
@@ -186,12 +198,17 @@ class Em:
             self.release(*key)
             return
         self.const_slots.pop(key, None)
+        if self.regs_only:
+            self.reg_state[key] = v
+            return
         idx = self.slot(*key)
         self.lines.append(f"{self.state_name}[{idx}*{self.stride_name}] = {v.s};")
 
     def load(self, key: Tuple) -> V:
         if key in self.const_slots:
             return const(self.const_slots[key])
+        if self.regs_only:
+            return self.reg_state[key]
         idx = self.slots[key]
         return self.tmp(f"{self.state_name}[{idx}*{self.stride_name}]")
 

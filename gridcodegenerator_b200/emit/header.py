@@ -9,6 +9,7 @@ plus  <algo>_launch  the stream-asynchronous launcher the C ABI binds.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Callable, List, Optional, Tuple
 
@@ -16,6 +17,8 @@ from . import algos
 from .spatial import Model
 
 SMEM_LIMIT = 232448 - 1024   # 227 KB opt-in maximum per CTA minus the per-CTA reservation
+MAX_WARPS = int(os.environ.get("GRID_MAX_WARPS", "8"))           # 65536 registers / (255 x 32)
+MAX_WARPS_SCRATCH = 4
 
 
 @dataclass
@@ -64,17 +67,21 @@ def specs(n: int) -> List[AlgoSpec]:
 def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     """(NT, STATE_SMEM, STAGED) for one algorithm and scalar size.
 
-    Single-warp CTAs (NT = 32): warps never talk to each other, so the smallest CTA gives the finest
-    shared-memory packing (resident warps per SM = floor(227 KB / bytes per warp)) and the best tail."""
-    NT = 32
+    One CTA per SM with as many warps as shared memory (per-thread state + per-warp TMA staging) and the
+    register file (255 registers/thread -> 8 warps) allow.  The warps of the CTA run in lockstep through the
+    straight-line body (GRID_SYNC points), which is what keeps the kernel off the instruction-fetch limit."""
     a16 = lambda x: (x + 15) & ~15
-    state = a16(slots * NT * sizeof)
-    stage = sum(2 * a16(32 * e * sizeof) for e in in_elems) + a16(32 * out_elems * sizeof) + 16
-    if state + stage + 16 <= SMEM_LIMIT:
-        return NT, True, True
-    if state + 16 <= SMEM_LIMIT:
-        return NT, True, False
-    return NT, False, False
+    state_w = a16(slots * 32 * sizeof)
+    stage_w = sum(2 * a16(32 * e * sizeof) for e in in_elems) + a16(32 * out_elems * sizeof) + 16
+    fit = (SMEM_LIMIT - 16) // (state_w + stage_w)
+    if os.environ.get("GRID_FORCE_UNSTAGED") == "1":
+        fit = 0
+    if fit >= 1:
+        return 32 * min(MAX_WARPS, fit), True, True
+    fit = (SMEM_LIMIT - 16) // state_w
+    if fit >= 1:
+        return 32 * min(MAX_WARPS, fit), True, False
+    return 32 * MAX_WARPS_SCRATCH, False, False
 
 
 def algo_struct_name(sp: AlgoSpec) -> str:

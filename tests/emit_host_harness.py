@@ -17,6 +17,8 @@ PRELUDE = """
 #define __device__
 #define __forceinline__ inline
 #define __restrict__
+#define GRID_FENCE() do { } while (0)
+#define GRID_SYNC() do { } while (0)
 namespace grid_rt { static inline void grid_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); } }
 """
 
