@@ -25,6 +25,35 @@ namespace grid_rt {
 __device__ __forceinline__ void grid_sincos(float x, float* s, float* c) { sincosf(x, s, c); }
 __device__ __forceinline__ void grid_sincos(double x, double* s, double* c) { sincos(x, s, c); }
 
+// ---- pairs of scalars: the dq / dqd derivative columns of a joint go through identical linear maps, so the
+// emitted bodies carry them as one P value.  For T = float P is float2 and every operation below is ONE packed
+// instruction on sm_100a (FFMA2 / FMUL2 / FADD2 with the scalar coefficient as a broadcast .F32 operand), which
+// halves the instruction stream of the gradient passes; for T = double it is two scalar operations.
+struct double_pair { double x, y; };
+template <typename T> struct pair_of;
+template <> struct pair_of<float> { typedef float2 type; };
+template <> struct pair_of<double> { typedef double_pair type; };
+template <typename T> using pair_t = typename pair_of<T>::type;
+
+template <typename T> __device__ __forceinline__ pair_t<T> mkp(T a, T b);
+template <> __device__ __forceinline__ float2 mkp<float>(float a, float b) { return make_float2(a, b); }
+template <> __device__ __forceinline__ double_pair mkp<double>(double a, double b) { double_pair r; r.x = a; r.y = b; return r; }
+template <typename T> __device__ __forceinline__ pair_t<T> pbc(T s) { return mkp<T>(s, s); }
+
+__device__ __forceinline__ float2 pfma(float2 a, float s, float2 c) { return __ffma2_rn(a, make_float2(s, s), c); }
+__device__ __forceinline__ float2 pmul(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }
+__device__ __forceinline__ float2 padd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 psub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }
+__device__ __forceinline__ float2 padds(float2 a, float s) { return __fadd2_rn(a, make_float2(s, s)); }
+__device__ __forceinline__ float2 pneg(float2 a) { return make_float2(-a.x, -a.y); }
+
+__device__ __forceinline__ double_pair pfma(double_pair a, double s, double_pair c) { double_pair r; r.x = fma(a.x, s, c.x); r.y = fma(a.y, s, c.y); return r; }
+__device__ __forceinline__ double_pair pmul(double_pair a, double s) { double_pair r; r.x = a.x * s; r.y = a.y * s; return r; }
+__device__ __forceinline__ double_pair padd(double_pair a, double_pair b) { double_pair r; r.x = a.x + b.x; r.y = a.y + b.y; return r; }
+__device__ __forceinline__ double_pair psub(double_pair a, double_pair b) { double_pair r; r.x = a.x - b.x; r.y = a.y - b.y; return r; }
+__device__ __forceinline__ double_pair padds(double_pair a, double s) { double_pair r; r.x = a.x + s; r.y = a.y + s; return r; }
+__device__ __forceinline__ double_pair pneg(double_pair a) { double_pair r; r.x = -a.x; r.y = -a.y; return r; }
+
 constexpr int TILE = 32;          // knot points per warp tile
 constexpr int MAX_STREAMS = 3;    // input arrays per algorithm (e.g. q_qd_u, qdd, Minv)
 
@@ -239,8 +268,11 @@ struct KernelPlan { const void* fn; int device; int blocks_per_sm; int sms; };
 // Persistent grid for a tile kernel: resident CTAs per SM (from the occupancy calculator, after opting in
 // to the large dynamic shared-memory carve-out) x SM count, clamped to the number of warp tiles.
 // Cached per (kernel, device); returns <= 0 on error (cudaGetLastError() holds the reason).
-inline int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int num_knots) {
-    static KernelPlan cache[64];
+// Internal linkage on purpose: several per-robot libraries live in one process (one .so per robot), and the
+// local statics of an `inline` function would be merged across them by the dynamic linker (STB_GNU_UNIQUE).
+static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int num_knots) {
+    constexpr int MAX_PLANS = 256;
+    static KernelPlan cache[MAX_PLANS];
     static int ncache = 0;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return -1;
@@ -253,7 +285,7 @@ inline int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem_bytes) != cudaSuccess) return -1;
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
         if (per_sm <= 0) { per_sm = 0; }
-        if (ncache >= 64) return -1;
+        if (ncache >= MAX_PLANS) ncache = 0;         // recycle: a plan is cheap to recompute
         cache[ncache] = KernelPlan{fn, dev, per_sm, sms};
         plan = &cache[ncache++];
     }
@@ -266,6 +298,6 @@ inline int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
 }
 
 // Number of CTAs the global state scratch attached to the robot model can serve (0 = none allocated).
-inline int& scratch_blocks() { static int v = 0; return v; }
+static int& scratch_blocks() { static int v = 0; return v; }
 
 }  // namespace grid_rt

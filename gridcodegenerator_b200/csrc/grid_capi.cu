@@ -157,6 +157,23 @@ int forward_dynamics_gradient_qdd_minv_impl(const T* d_q_qd, int stride, const T
                                                                    static_cast<cudaStream_t>(s)), fn);
 }
 
+template <typename T>
+int aba_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
+    const char* fn = "grid_aba";
+    if (nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd))) return bad_arg(fn, "bad pointer / stride / num_knots");
+    auto* m = models<T>().get();
+    if (!m) return bad_arg(fn, "no CUDA device");
+    return fail(grid::aba_launch<T>(d_qdd, d_in, stride, m, g, nk, static_cast<cudaStream_t>(s)), fn);
+}
+template <typename T>
+int crba_impl(const T* d_q, int stride, T* d_M, int nk, void* s) {
+    const char* fn = "grid_crba";
+    if (nk < 0 || stride < N || (nk > 0 && (!d_q || !d_M))) return bad_arg(fn, "bad pointer / stride / num_knots");
+    auto* m = models<T>().get();
+    if (!m) return bad_arg(fn, "no CUDA device");
+    return fail(grid::crba_launch<T>(d_M, d_q, stride, m, T(0), nk, static_cast<cudaStream_t>(s)), fn);
+}
+
 // ---- host-buffer pipeline: chunks of the batch rotate over three streams so that the H2D copy of
 // chunk i+1, the kernel of chunk i and the D2H copy of chunk i-1 overlap (PCIe is full duplex).
 template <typename T, class Launch>
@@ -223,6 +240,10 @@ long kernel_info(int algo, int what) {
                        static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
         GRID_INFO_CASE(7, forward_dynamics_gradient_qdd_minv_cfg, forward_dynamics_gradient_qdd_minv_algo,
                        static_cast<void (*)(T*, const T*, const int, const T*, const T*, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
+        GRID_INFO_CASE(8, aba_cfg, aba_algo,
+                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(aba_kernel<T>))
+        GRID_INFO_CASE(9, crba_cfg, crba_algo,
+                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(crba_kernel<T>))
     }
     return -1;
 }
@@ -251,6 +272,8 @@ long grid_kernel_info(int algo, int is_f64, int what) {
     int grid_forward_dynamics_gradient_qdd_minv_##SUF(const T* a, int st, const T* b, const T* c, T* o, int nk,   \
                                                       T g, void* s) {                                              \
         return forward_dynamics_gradient_qdd_minv_impl<T>(a, st, b, c, o, nk, g, s); }                             \
+    int grid_aba_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return aba_impl<T>(a, st, o, nk, g, s); }  \
+    int grid_crba_##SUF(const T* a, int st, T* o, int nk, void* s) { return crba_impl<T>(a, st, o, nk, s); }      \
     int grid_forward_dynamics_gradient_host_##SUF(const T* h_in, T* h_out, int nk, T g) {                          \
         return host_pipeline<T>("grid_forward_dynamics_gradient_host", h_in, 3 * N, h_out, 2 * N * N, nk,          \
             [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \

@@ -189,9 +189,12 @@ def _sym_load(em: Em, name, j):
     return M
 
 
-def articulated_inertias(cx: Ctx):
+def articulated_inertias(cx: Ctx, bias=None):
     """Backward recursion IA_p += X^T (IA - U D^-1 U^T) X (reference _test.py:117-184 without the F part,
-    algorithms/_direct_minv.py:127-148, :226-337).  Stores U_j (6) and 1/D_j in the state."""
+    algorithms/_direct_minv.py:127-148, :226-337).  Stores U_j (6) and 1/D_j in the state.
+
+    bias(j, IA, U, Dinv, UD, Ia): optional hook called once per joint with the final articulated inertia
+    (Ia and UD are None for base-rooted joints); ABA uses it to propagate the bias force alongside."""
     em, m = cx.em, cx.m
     carry: Dict[int, List[List[V]]] = {}
     in_state: Dict[int, bool] = {}
@@ -215,6 +218,8 @@ def articulated_inertias(cx: Ctx):
         em.store_vec("U", j, U)
         em.store(("Dinv", j, 0), Dinv)
         if p < 0:
+            if bias is not None:
+                bias(j, IA, U, Dinv, None, None)
             continue
         UD = [em.mul(U[r], Dinv) for r in range(6)]
         Ia = [[None] * 6 for _ in range(6)]
@@ -225,6 +230,8 @@ def articulated_inertias(cx: Ctx):
                 else:
                     Ia[r][k] = em.lincomb([(1.0, IA[r][k]), (-1.0, UD[r], U[k])])
                 Ia[k][r] = Ia[r][k]
+        if bias is not None:
+            bias(j, IA, U, Dinv, UD, Ia)
         XtIaX = cx.X[j].congruence(em, Ia)
         if p == j - 1:
             carry[p] = XtIaX
@@ -314,21 +321,48 @@ def fd_finish(cx: Ctx, Minv, u: Sequence[V], c: Sequence[V]) -> List[V]:
 
 
 # ============================================================== grad RNEA
-def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
-    """Analytical dc/dq and dc/dqd, one derivative column c at a time (both the q and the qd column of joint c
-    are carried together for ILP).  Needs v, Iv, Xa and the accumulated f in the state (rnea_forward(keep=True)
-    + rnea_backward(keep_f=True)).  Follows reference _test.py:229-488; the column of joint c touches only
-    subtree(c) (forward) and subtree(c) + ancestors(c) (backward), which is the reference's column
-    compression (algorithms/_inverse_dynamics_gradient.py:55-98) made static.
+def pairs_policy() -> bool:
+    """Carry the dq and dqd derivative columns of a joint as one packed pair (FFMA2 on sm_100a)."""
+    return os.environ.get("GRID_EMIT_PAIRS", "1") != "0"
 
-    sink(c, dc_dq_col, dc_dqd_col): lists of n V's (structural zeros are constants)."""
+
+def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
+    """Analytical dc/dq and dc/dqd, one derivative column c at a time.  Needs v, Iv, Xa and the accumulated f in
+    the state (rnea_forward(keep=True) + rnea_backward(keep_f=True)).  Follows reference _test.py:229-488; the
+    column of joint c touches only subtree(c) (forward) and subtree(c) + ancestors(c) (backward), which is the
+    reference's column compression (algorithms/_inverse_dynamics_gradient.py:55-98) made static.
+
+    The q column and the qd column of joint c obey the same linear recursions with different seeds, so they are
+    carried as ONE pair-valued column (x = d/dq_c, y = d/dqd_c): every multiply-add on it is a packed FFMA2.
+
+    sink(c, dc): list of n V's, pair-valued (x: dc/dq_c, y: dc/dqd_c); structural zeros are constants."""
     em, m = cx.em, cx.m
     n = m.n
+    packed = pairs_policy()
+
+    def pk(a: Sequence[V], b: Sequence[V]) -> List:
+        return [em.mkpair(x, y) for x, y in zip(a, b)] if packed else [(x, y) for x, y in zip(a, b)]
+
+    # unpacked fallback = two scalar columns run through the same code (tuple-valued entries)
+    def lift(fn):
+        def run(*vecs, **kw):
+            if packed:
+                return fn(*vecs, **kw)
+            outs = []
+            for h in (0, 1):
+                args = [[e[h] if isinstance(e, tuple) else e for e in vec] if isinstance(vec, list) else vec for vec in vecs]
+                kws = {k: ([e[h] if isinstance(e, tuple) else e for e in v] if isinstance(v, list) else v) for k, v in kw.items()}
+                outs.append(fn(*args, **kws))
+            return [(x, y) for x, y in zip(*outs)]
+        return run
+
     for c in range(n):
         em.comment(f"grad RNEA column {c}")
         sub = m.subtree[c]
         DV: Dict[int, tuple] = {}
-        ps_q, ps_d = Pusher(em, ("dfq", c)), Pusher(em, ("dfd", c))
+        ps = Pusher(em, ("df", c))
+        if not packed:
+            ps = _TuplePusher(em, ("df", c))
         last = sub[-1]
         for j in sub:
             jd = m.joints[j]
@@ -343,47 +377,117 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
                 dvd = unit(S, ONE)
                 daq = [em.add(x, y) for x, y in zip(mxS(em, S, dvq, qd[j]), mxS(em, S, Xa))]
                 dad = mxS(em, S, v)                                         # mxS(S) qd = 0
+                dv, da = pk(dvq, dvd), pk(daq, dad)
             else:
-                pdvq, pdvd, pdaq, pdad = DV[jd.parent]
-                dvq = cx.X[j].apply(em, pdvq)
-                dvd = cx.X[j].apply(em, pdvd)
-                daq = [em.add(x, y) for x, y in zip(cx.X[j].apply(em, pdaq), mxS(em, S, dvq, qd[j]))]
-                dad = [em.add(x, y) for x, y in zip(cx.X[j].apply(em, pdad), mxS(em, S, dvd, qd[j]))]
+                pdv, pda = DV[jd.parent]
+                dv = lift(lambda x: cx.X[j].apply(em, x))(pdv)
+                da = lift(lambda xa, xv: [em.add(x, y) for x, y in zip(cx.X[j].apply(em, xa), mxS(em, S, xv, qd[j]))])(pda, dv)
             if m.children[j]:
-                DV[j] = (dvq, dvd, daq, dad)
+                DV[j] = (dv, da)
             # df = dv x* Iv + I da + v x* (I dv)      (reference _test.py:389-424)
-            dfq = fxv(em, v, inertia_mul(em, jd.I, dvq), acc=fxv(em, dvq, Iv, acc=inertia_mul(em, jd.I, daq)))
-            dfd = fxv(em, v, inertia_mul(em, jd.I, dvd), acc=fxv(em, dvd, Iv, acc=inertia_mul(em, jd.I, dad)))
+            df = lift(lambda xv, xa: fxv(em, v, inertia_mul(em, jd.I, xv),
+                                         acc=fxv(em, xv, Iv, acc=inertia_mul(em, jd.I, xa))))(dv, da)
             if j == last and not m.children[j]:
-                ps_q.carry[j], ps_d.carry[j] = dfq, dfd   # consumed immediately by the backward sweep
+                ps.carry[j] = df   # consumed immediately by the backward sweep
             else:
-                ps_q.set_base(j, dfq)
-                ps_d.set_base(j, dfd)
-        dcq: List[V] = [ZERO] * n
-        dcd: List[V] = [ZERO] * n
+                ps.set_base(j, df)
+        dc: List = [ZERO] * n
         rel = sorted(set(sub) | set(m.ancestors[c]), reverse=True)
         em.comment(f"grad RNEA column {c}, backward sweep")
         for j in rel:
             jd = m.joints[j]
-            fq, fd_ = ps_q.pull(j), ps_d.pull(j)
-            dcq[j] = fq[jd.S]
-            dcd[j] = fd_[jd.S] if j != c else em.lincomb([(1.0, fd_[jd.S])], const(jd.damping))
+            f = ps.pull(j)
+            dc[j] = f[jd.S]
+            if j == c and jd.damping != 0.0:
+                if packed:
+                    dc[j] = em.add(f[jd.S], em.mkpair(ZERO, const(jd.damping)))
+                else:
+                    dc[j] = (f[jd.S][0], em.lincomb([(1.0, f[jd.S][1])], const(jd.damping)))
             if jd.parent >= 0:
                 if j == c:
-                    Mxf = mxS(em, jd.S, em.load_vec("f", j))
-                    fq = [em.sub(x, y) for x, y in zip(fq, Mxf)]             # - X^T mxS(f) (reference :434-437)
-                ps_q.push(jd.parent, j, lambda acc, f=fq, j=j: cx.X[j].applyT(em, f, acc=acc))
-                ps_d.push(jd.parent, j, lambda acc, f=fd_, j=j: cx.X[j].applyT(em, f, acc=acc))
+                    Mxf = mxS(em, jd.S, em.load_vec("f", j))                  # - X^T mxS(f) (reference :434-437)
+                    if packed:
+                        f = [em.sub(x, em.mkpair(y, ZERO)) for x, y in zip(f, Mxf)]
+                    else:
+                        f = [(em.sub(x[0], y), x[1]) for x, y in zip(f, Mxf)]
+                ps.push(jd.parent, j, lambda acc, f=f, j=j: lift(lambda ff, acc=None: cx.X[j].applyT(em, ff, acc=acc))(f, acc=acc))
         for j in rel:
-            em.release_vec(("dfq", c), j)
-            em.release_vec(("dfd", c), j)
-        sink(c, dcq, dcd)
+            em.release_vec(("df", c), j)
+            if not packed:
+                em.release_vec(("df", c, 1), j)
+        sink(c, dc)
+
+
+class _TuplePusher(Pusher):
+    """Pusher over (q, qd) tuples of scalars: the unpacked (GRID_EMIT_PAIRS=0) form of a pair column."""
+
+    def __init__(self, em, name):
+        super().__init__(em, name)
+        self.h = [Pusher(em, name), Pusher(em, name + (1,))]
+
+    def set_base(self, j, vec):
+        for h in (0, 1):
+            self.h[h].set_base(j, [e[h] for e in vec])
+
+    def push(self, p, j, fn):
+        # fn(acc) works on tuple vectors; run it once with tuple accumulators and scatter the halves
+        if p == j - 1:
+            self.carry[p] = fn(self.carry.get(p))
+            return
+        base = None
+        if self.h[0].in_state.get(p):
+            base = [(x, y) for x, y in zip(self.em.load_vec(self.h[0].name, p), self.em.load_vec(self.h[1].name, p))]
+        out = fn(base)
+        for h in (0, 1):
+            self.em.store_vec(self.h[h].name, p, [e[h] for e in out])
+            self.h[h].in_state[p] = True
+
+    def pull(self, j):
+        base = None
+        if self.h[0].in_state.get(j):
+            base = [(x, y) for x, y in zip(self.em.load_vec(self.h[0].name, j), self.em.load_vec(self.h[1].name, j))]
+        c = self.carry.pop(j, None)
+        if base is None and c is None:
+            return [(ZERO, ZERO)] * 6
+        if base is None:
+            return list(c)
+        if c is None:
+            return base
+        return [(self.em.add(a[0], b[0]), self.em.add(a[1], b[1])) for a, b in zip(base, c)]
+
+    @property
+    def carry(self):
+        return self.__dict__.setdefault("_carry", {})
+
+    @carry.setter
+    def carry(self, v):
+        self.__dict__["_carry"] = v
+
+
+def _halves(em: Em, e):
+    """(x, y) scalar views of a pair-valued entry (pair V, tuple of scalars, or a broadcast scalar)."""
+    if isinstance(e, tuple):
+        return e
+    return em.half(e, 0), em.half(e, 1)
 
 
 # ============================================================ kernel bodies
 def _out(em: Em, idx: int, v: V, ptr: str = "o"):
     from .core import lit
     em.line(f"{ptr}[{idx}] = {lit(v.c) if v.is_const else v.s};")
+
+
+def _sink_product(em: Em, n: int, c_: int, dc, minv):
+    """Columns c_ and n + c_ of df_du = -Minv dc_du (reference algorithms/_forward_dynamics_gradient.py:48-62)."""
+    if all(not isinstance(e, tuple) for e in dc):
+        for r in range(n):
+            x, y = _halves(em, em.lincomb([(-1.0, minv(r, k), dc[k]) for k in range(n)]))
+            _out(em, c_ * n + r, x)
+            _out(em, (n + c_) * n + r, y)
+        return
+    for r in range(n):
+        for h in (0, 1):
+            _out(em, (h * n + c_) * n + r, em.lincomb([(-1.0, minv(r, k), _halves(em, dc[k])[h]) for k in range(n)]))
 
 
 class Body:
@@ -444,10 +548,11 @@ def body_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> Body:
     rnea_forward(cx, qd, qdd, keep=True)
     rnea_backward(cx, qd, keep_f=True)
 
-    def sink(c, dcq, dcd):
+    def sink(c, dc):
         for r in range(n):
-            _out(cx.em, c * n + r, dcq[r])
-            _out(cx.em, (n + c) * n + r, dcd[r])
+            x, y = _halves(cx.em, dc[r])
+            _out(cx.em, c * n + r, x)
+            _out(cx.em, (n + c) * n + r, y)
 
     rnea_grad_columns(cx, qd, sink)
     return Body("inverse_dynamics_gradient_inner", "", cx, "[dc/dq | dc/dqd], column-major n x 2n")
@@ -473,11 +578,9 @@ def body_forward_dynamics_gradient(model: Model) -> Body:
     rnea_backward(cx, qd, keep_f=True)
     em.comment("---- grad RNEA columns and df_du = -Minv dc_du")
 
-    def sink(c_, dcq, dcd):
+    def sink(c_, dc):
         Mi = load_minv(cx, keys)
-        for r in range(n):
-            _out(em, c_ * n + r, em.lincomb([(-1.0, minv_get(Mi, r, k), dcq[k]) for k in range(n)]))
-            _out(em, (n + c_) * n + r, em.lincomb([(-1.0, minv_get(Mi, r, k), dcd[k]) for k in range(n)]))
+        _sink_product(em, n, c_, dc, lambda r, k: minv_get(Mi, r, k))
 
     rnea_grad_columns(cx, qd, sink)
     return Body("forward_dynamics_gradient_inner", "", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]")
@@ -494,11 +597,132 @@ def body_forward_dynamics_gradient_qdd_minv(model: Model) -> Body:
     rnea_forward(cx, qd, qdd, keep=True)
     rnea_backward(cx, qd, keep_f=True)
 
-    def sink(c_, dcq, dcd):
+    def sink(c_, dc):
         Mi = [[em.tmp(f"Minv[{k * n + r}]") for k in range(n)] for r in range(n)]
-        for r in range(n):
-            _out(em, c_ * n + r, em.lincomb([(-1.0, Mi[r][k], dcq[k]) for k in range(n)]))
-            _out(em, (n + c_) * n + r, em.lincomb([(-1.0, Mi[r][k], dcd[k]) for k in range(n)]))
+        _sink_product(em, n, c_, dc, lambda r, k: Mi[r][k])
 
     rnea_grad_columns(cx, qd, sink)
     return Body("forward_dynamics_gradient_inner", "", cx, "-Minv [dc/dq | dc/dqd] with qdd and Minv supplied")
+
+
+# ===================================================================== ABA
+def body_aba(model: Model) -> Body:
+    """qdd by the articulated-body algorithm (reference algorithms/_aba.py:46-407; Featherstone RBDA table 7.1).
+    Differences from the reference's emitted code, all in favour of the oracle: the
+    velocity-product term uses each joint's own axis (the reference hard-codes mx2, _aba.py:123), joint damping
+    is included (so that ABA == Minv (u - c) with the oracle's c), child contributions are accumulated in a
+    fixed order instead of shared-memory atomics (_aba.py:290, :307)."""
+    cx = Ctx(model)
+    em, m, n = cx.em, model, model.n
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    tau = cx.read_vec("u", "tau_")
+    nonadj_parent = {p for j, p in enumerate(m.parent) if p >= 0 and p != j - 1}
+    V_: Dict[int, List[V]] = {}
+    pAs = Pusher(em, "pA")
+    for j, jd in enumerate(m.joints):
+        em.comment(f"ABA forward 1, joint {j}")
+        p, S = jd.parent, jd.S
+        if p >= 0:
+            vp = V_[p] if p == j - 1 else em.load_vec("v", p)
+            v = cx.X[j].apply(em, vp)
+            v[S] = em.add(v[S], qd[j])
+            c = mxS(em, S, v, qd[j])
+        else:
+            v = unit(S, qd[j])
+            c = [ZERO] * 6
+        em.store_vec("c", j, c)
+        pAs.set_base(j, fxv(em, v, inertia_mul(em, jd.I, v)))
+        if j in nonadj_parent:
+            em.store_vec("v", j, v)
+        V_[j] = v
+        V_.pop(j - 2, None)
+
+    def bias(j, IA, U, Dinv, UD, Ia):
+        jd = m.joints[j]
+        pA = pAs.pull(j)
+        uu = em.lincomb([(1.0, tau[j]), (-jd.damping, qd[j]), (-1.0, pA[jd.S])])
+        em.store(("uu", j, 0), uu)
+        if jd.parent < 0:
+            return
+        c = em.load_vec("c", j)
+        w = em.mul(uu, Dinv)
+        pa = [em.lincomb([(1.0, Ia[r][k], c[k]) for k in range(6)] + [(1.0, U[r], w)], pA[r]) for r in range(6)]
+        pAs.push(jd.parent, j, lambda acc, pa=pa, j=j: cx.X[j].applyT(em, pa, acc=acc))
+
+    articulated_inertias(cx, bias=bias)
+    A_: Dict[int, List[V]] = {}
+    grav = [ZERO] * 5 + [cx.gravity]
+    for j, jd in enumerate(m.joints):
+        em.comment(f"ABA forward 2, joint {j}")
+        p, S = jd.parent, jd.S
+        if p >= 0:
+            apar = A_[p] if p == j - 1 else em.load_vec("a", p)
+        else:
+            apar = grav
+        ap = em.vadd(cx.X[j].apply(em, apar), em.load_vec("c", j))
+        U, Dinv, uu = em.load_vec("U", j), em.load(("Dinv", j, 0)), em.load(("uu", j, 0))
+        qddj = em.mul(em.lincomb([(-1.0, U[r], ap[r]) for r in range(6)], uu), Dinv)
+        _out(em, j, qddj)
+        a = list(ap)
+        a[S] = em.add(a[S], qddj)
+        if j in nonadj_parent:
+            em.store_vec("a", j, a)
+        A_[j] = a
+        A_.pop(j - 2, None)
+    return Body("aba_inner", "", cx, "qdd = ABA(q, qd, tau)")
+
+
+# ===================================================================== CRBA
+def body_crba(model: Model) -> Body:
+    """Joint-space inertia matrix M(q), full symmetric, column-major (reference algorithms/_crba.py:30-209;
+    Featherstone RBDA table 6.2).  The composite inertia of joint j is final once all its descendants (ids > j,
+    DFS pre-order) have been folded in, so column j of M is produced right there by walking f_h = IC_j S up the
+    ancestor chain; composite inertias live in their own storage (the reference accumulates them into the shared
+    I table, _crba.py:81-143, and hard-codes n = 7 offsets)."""
+    cx = Ctx(model)
+    em, m, n = cx.em, model, model.n
+    cx.prologue()
+    carry: Dict[int, List[List[V]]] = {}
+    in_state: Dict[int, bool] = {}
+    Mv: Dict[tuple, V] = {}
+    for j in range(n - 1, -1, -1):
+        jd = m.joints[j]
+        em.comment(f"CRBA, joint {j}")
+        IC = [[const(jd.I[r, k]) for k in range(6)] for r in range(6)]
+        extra = []
+        if in_state.get(j):
+            extra.append(_sym_load(em, "IC", j))
+        if j in carry:
+            extra.append(carry.pop(j))
+        for E in extra:
+            for r in range(6):
+                for k in range(r, 6):
+                    IC[r][k] = em.add(IC[r][k], E[r][k])
+                    IC[k][r] = IC[r][k]
+        fh = [IC[r][jd.S] for r in range(6)]
+        Mv[(j, j)] = fh[jd.S]
+        i = j
+        while m.parent[i] >= 0:
+            fh = cx.X[i].applyT(em, fh)
+            i = m.parent[i]
+            Mv[(i, j)] = fh[m.joints[i].S]
+        p = jd.parent
+        if p < 0:
+            continue
+        XtIX = cx.X[j].congruence(em, IC)
+        if p == j - 1:
+            carry[p] = XtIX
+        else:
+            if in_state.get(p):
+                old = _sym_load(em, "IC", p)
+                XtIX = [[em.add(old[r][k], XtIX[r][k]) if k >= r else None for k in range(6)] for r in range(6)]
+                for r in range(6):
+                    for k in range(r):
+                        XtIX[r][k] = XtIX[k][r]
+            _sym_store(em, "IC", p, XtIX)
+            in_state[p] = True
+    for col in range(n):
+        for r in range(n):
+            _out(em, col * n + r, Mv.get((min(r, col), max(r, col)), ZERO))
+    return Body("crba_inner", "", cx, "M(q), dense symmetric, column-major")

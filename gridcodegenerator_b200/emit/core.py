@@ -16,13 +16,17 @@ Number = Union[int, float]
 
 
 class V:
-    """A scalar: compile-time constant (`c`) or a C identifier/expression (`s`)."""
+    """A scalar: compile-time constant (`c`) or a C identifier/expression (`s`).
+    With `p` the identifier names a PAIR of scalars (type P = grid_rt::pair_t<T>: float2 for T = float, so that
+    linear combinations of pairs with scalar coefficients become packed FFMA2 / FMUL2 / FADD2 on sm_100a).
+    A scalar used where a pair is expected means the broadcast (s, s)."""
 
-    __slots__ = ("c", "s")
+    __slots__ = ("c", "s", "p")
 
-    def __init__(self, c: Optional[float] = None, s: Optional[str] = None):
+    def __init__(self, c: Optional[float] = None, s: Optional[str] = None, p: bool = False):
         self.c = None if c is None else float(c)
         self.s = s
+        self.p = p
 
     @property
     def is_const(self):
@@ -89,6 +93,28 @@ class Em:
         self.lines.append(f"const T {name} = {expr};")
         return V(s=name)
 
+    def tmp2(self, expr: str) -> V:
+        name = f"t{self.ctr}"
+        self.ctr += 1
+        self.lines.append(f"const P {name} = {expr};")
+        return V(s=name, p=True)
+
+    def mkpair(self, a: V, b: V) -> V:
+        """The pair (a, b) of two scalars (constants allowed)."""
+        if a.p or b.p:
+            raise ValueError("mkpair takes scalars")
+        if a.is_const and b.is_const and a.c == b.c:
+            return a                      # broadcast constant (covers the structural zero)
+        ea = lit(a.c) if a.is_const else a.s
+        eb = lit(b.c) if b.is_const else b.s
+        return self.tmp2(f"grid_rt::mkp<T>({ea}, {eb})")
+
+    def half(self, v: V, which: int) -> V:
+        """Component 0 / 1 of a pair (a scalar stands for (s, s))."""
+        if not v.p:
+            return v
+        return V(s=f"{v.s}.{'xy'[which]}")
+
     def named(self, name: str, expr: str) -> V:
         self.lines.append(f"const T {name} = {expr};")
         return V(s=name)
@@ -100,6 +126,8 @@ class Em:
     def lincomb(self, terms: Sequence[Tuple], acc: Optional[V] = None) -> V:
         """sum_k coef_k * x_k [* y_k] (+ acc).  terms: (coef, x) or (coef, x, y) with coef a Python
         float and x, y V's.  Constants are folded; emits at most one statement."""
+        if (acc is not None and acc.p) or any(v is not None and v.p for t in terms for v in t[1:]):
+            return self._lincomb2(terms, acc)
         csum = 0.0
         parts: List[Tuple[float, str]] = []
         if acc is not None:
@@ -144,6 +172,83 @@ class Em:
             self.n_ops += 1
         return self.tmp("".join(out))
 
+    def _lincomb2(self, terms: Sequence[Tuple], acc: Optional[V]) -> V:
+        """Pair-valued lincomb: every term has at most one pair factor, the rest are scalar coefficients."""
+        csum = 0.0
+        expr: Optional[str] = None
+        bparts: List[Tuple[float, str]] = []           # scalar (broadcast) terms
+        pparts: List[Tuple[float, List[str], str]] = []
+        if acc is not None:
+            if acc.is_const:
+                csum += acc.c
+            elif acc.p:
+                expr = acc.s
+            else:
+                bparts.append((1.0, acc.s))
+        for t in terms:
+            coef = float(t[0])
+            names: List[str] = []
+            pn: Optional[str] = None
+            for v in t[1:]:
+                if v is None:
+                    continue
+                if v.is_const:
+                    coef *= v.c
+                elif v.p:
+                    if pn is not None:
+                        raise ValueError("product of two pairs in a linear combination")
+                    pn = v.s
+                else:
+                    names.append(v.s)
+            if coef == 0.0:
+                continue
+            if pn is None:
+                if not names:
+                    csum += coef
+                else:
+                    bparts.append((coef, "*".join(names)))
+            else:
+                pparts.append((coef, names, pn))
+        if expr is None and len(pparts) == 1 and not bparts and csum == 0.0 and pparts[0][0] == 1.0 and not pparts[0][1]:
+            return V(s=pparts[0][2], p=True)
+        pparts.sort(key=lambda q: q[0] < 0)
+        for coef, names, pn in pparts:
+            mag = abs(coef)
+            unity = mag == 1.0 and not names
+            sc = "*".join(([lit(mag)] if mag != 1.0 else []) + names)
+            self.n_ops += max(len(names) - 1 + (mag != 1.0), 0)      # scalar multiplies forming the coefficient
+            if expr is None:
+                if unity:
+                    expr = pn if coef > 0 else f"grid_rt::pneg({pn})"
+                else:
+                    expr = f"grid_rt::pmul({pn}, {sc})" if coef > 0 else f"grid_rt::pmul({pn}, -({sc}))"
+                    self.n_ops += 2
+            else:
+                if unity:
+                    expr = f"grid_rt::padd({expr}, {pn})" if coef > 0 else f"grid_rt::psub({expr}, {pn})"
+                    self.n_ops += 2
+                else:
+                    expr = f"grid_rt::pfma({pn}, {sc}, {expr})" if coef > 0 else f"grid_rt::pfma({pn}, -({sc}), {expr})"
+                    self.n_ops += 4
+        if bparts or csum != 0.0:
+            out = []
+            bparts.sort(key=lambda q: q[0] < 0)
+            for i, (coef, name) in enumerate(bparts):
+                mag = abs(coef)
+                body = name if mag == 1.0 else f"{lit(mag)}*{name}"
+                if i == 0:
+                    out.append(body if coef > 0 else f"-{body}")
+                else:
+                    out.append((" + " if coef > 0 else " - ") + body)
+            if csum != 0.0:
+                out.append(((" + " if csum > 0 else " - ") if out else ("" if csum > 0 else "-")) + lit(abs(csum)))
+            b = "".join(out)
+            expr = f"grid_rt::pbc<T>({b})" if expr is None else f"grid_rt::padds({expr}, {b})"
+            self.n_ops += 2
+        if expr is None:
+            return const(0.0)
+        return self.tmp2(expr)
+
     def add(self, a: V, b: V) -> V:
         return self.lincomb([(1.0, a), (1.0, b)])
 
@@ -187,9 +292,10 @@ class Em:
 
     def release(self, *key):
         """Return a slot to the pool (its value is dead from here on)."""
-        idx = self.slots.pop(key, None)
-        if idx is not None:
-            self.free.append(idx)
+        for k in (key, key + ("x",), key + ("y",)):
+            idx = self.slots.pop(k, None)
+            if idx is not None:
+                self.free.append(idx)
 
     def store(self, key: Tuple, v: V):
         """Store v into the state slot `key`; constants are remembered at emit time, not stored."""
@@ -201,6 +307,18 @@ class Em:
         if self.regs_only:
             self.reg_state[key] = v
             return
+        if v.p:
+            idx = self.slots.pop(key, None)
+            if idx is not None:
+                self.free.append(idx)
+            for h in "xy":
+                idx = self.slot(*(key + (h,)))
+                self.lines.append(f"{self.state_name}[{idx}*{self.stride_name}] = {v.s}.{h};")
+            return
+        for h in "xy":
+            idx = self.slots.pop(key + (h,), None)
+            if idx is not None:
+                self.free.append(idx)
         idx = self.slot(*key)
         self.lines.append(f"{self.state_name}[{idx}*{self.stride_name}] = {v.s};")
 
@@ -209,6 +327,10 @@ class Em:
             return const(self.const_slots[key])
         if self.regs_only:
             return self.reg_state[key]
+        if key not in self.slots and (key + ("x",)) in self.slots:
+            ix, iy = self.slots[key + ("x",)], self.slots[key + ("y",)]
+            return self.tmp2(f"grid_rt::mkp<T>({self.state_name}[{ix}*{self.stride_name}], "
+                             f"{self.state_name}[{iy}*{self.stride_name}])")
         idx = self.slots[key]
         return self.tmp(f"{self.state_name}[{idx}*{self.stride_name}]")
 

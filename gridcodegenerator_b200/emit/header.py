@@ -61,6 +61,10 @@ def specs(n: int) -> List[AlgoSpec]:
                  algos.body_forward_dynamics_gradient_qdd_minv,
                  ["q", "qd", "qdd", "Minv"], [("d_q_qd", 2 * n), ("d_qdd", n), ("d_Minv", n * n)],
                  [(0, 0), (0, n), (1, 0), (2, 0)], "d_df_du", lambda n: 2 * n * n),
+        AlgoSpec("aba", "aba", "ABA", "", algos.body_aba,
+                 ["q", "qd", "u"], [("d_q_qd_tau", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_qdd", lambda n: n),
+        AlgoSpec("crba", "crba", "CRBA", "", algos.body_crba,
+                 ["q"], [("d_q_qd", n)], [(0, 0)], "d_M", lambda n: n * n),
     ]
 
 
@@ -96,7 +100,7 @@ def emit_inner(sp: AlgoSpec, body: algos.Body) -> str:
            f" * Emitted operations (mul+add): {body.n_ops}\n */\n")
     head = (f"template <typename T, int NT>\n__device__ __forceinline__\n"
             f"void {sp.fn}_inner(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n")
-    return doc + head + "    using grid_rt::grid_sincos;\n" + body.code + "}\n\n"
+    return doc + head + "    using grid_rt::grid_sincos;\n    typedef grid_rt::pair_t<T> P;\n" + body.code + "}\n\n"
 
 
 def emit_algo_struct(sp: AlgoSpec, body: algos.Body, n: int) -> str:
@@ -277,6 +281,14 @@ def host_specs(n: int) -> List[HostSpec]:
                  ["if (USE_QDD_MINV_FLAG) err = forward_dynamics_gradient_qdd_minv_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, hd_data->d_qdd, hd_data->d_Minv, d_robotModel, gravity, num_timesteps, 0);",
                   "else err = forward_dynamics_gradient_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
                  ("hd_data->d_df_du", "hd_data->h_df_du", "2*NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("aba", "", "ABA", True, ["const int stride_q_qd = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd")],
+                 ["err = aba_launch<T>(hd_data->d_qdd, hd_data->d_q_qd_u, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS")),
+        HostSpec("crba", ", bool USE_COMPRESSED_MEM = false", "CRBA", True, comp,
+                 [("", "d_in", "h_in", "stride_q_qd")],
+                 ["err = crba_launch<T>(hd_data->d_M, d_in, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_M", "hd_data->h_M", "NUM_JOINTS*NUM_JOINTS")),
     ]
 
 

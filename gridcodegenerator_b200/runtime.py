@@ -27,7 +27,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
               "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
-              "forward_dynamics_gradient_qdd_minv": 7}
+              "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9}
 
 
 def _nvcc() -> str:
@@ -115,6 +115,8 @@ class GRiDLibrary:
             getattr(L, f"grid_forward_dynamics_gradient_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_forward_dynamics_gradient_qdd_minv_{suf}").argtypes = [vp, ci, vp, vp, vp, ci, g, vp]
             getattr(L, f"grid_forward_dynamics_gradient_host_{suf}").argtypes = [vp, vp, ci, g]
+            getattr(L, f"grid_aba_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_crba_{suf}").argtypes = [vp, ci, vp, ci, vp]
         L.grid_forward_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
         L.grid_inverse_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
 
@@ -227,6 +229,26 @@ class GRiDLibrary:
         with torch.cuda.device(q_qd.device):
             self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_qdd_minv_{suf}")(
                 p, stride, pq, pm, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def aba(self, q_qd_tau, gravity: float = 9.81, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd_tau, 3 * n)
+        suf = self._suf(q_qd_tau)
+        out = torch.empty((B, n), dtype=q_qd_tau.dtype, device=q_qd_tau.device) if out is None else out
+        with torch.cuda.device(q_qd_tau.device):
+            self._check(getattr(self.lib, f"grid_aba_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def crba(self, q, out=None):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q, n)
+        suf = self._suf(q)
+        out = torch.empty((B, n * n), dtype=q.dtype, device=q.device) if out is None else out
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_crba_{suf}")(p, stride, out.data_ptr(), B, self._stream()))
         return out
 
     # --------------------------------------------------------- host entry points

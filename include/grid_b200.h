@@ -32,7 +32,8 @@ const char *grid_robot_name(void);
 const char *grid_last_error(void);
 int grid_abi_version(void);
 /* shared-memory bytes per CTA, threads per CTA, per-thread state elements of an algorithm's kernel
- * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv); is_f64: 0/1
+ * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv), 8 ABA, 9 CRBA;
+ * is_f64: 0/1
  * what: 0 smem bytes, 1 threads, 2 state slots, 3 state in shared memory (0/1), 4 TMA-staged I/O (0/1),
  *       5 persistent grid size for num_knots = 1<<20 on the current device */
 long grid_kernel_info(int algo, int is_f64, int what);
@@ -79,6 +80,17 @@ int grid_forward_dynamics_gradient_qdd_minv_f32(const float *d_q_qd, int stride,
 int grid_forward_dynamics_gradient_qdd_minv_f64(const double *d_q_qd, int stride, const double *d_qdd,
                                                 const double *d_Minv, double *d_df_du, int num_knots,
                                                 double gravity, void *stream);
+
+/* ---- forward dynamics by the articulated-body algorithm, qdd n per knot; d_q_qd_tau: [q|qd|tau]
+ * replaces aba<T> (algorithms/_aba.py:539-596; kernel :482-537) */
+int grid_aba_f32(const float *d_q_qd_tau, int stride, float *d_qdd, int num_knots, float gravity, void *stream);
+int grid_aba_f64(const double *d_q_qd_tau, int stride, double *d_qdd, int num_knots, double gravity, void *stream);
+
+/* ---- joint-space inertia matrix M(q) by the composite-rigid-body algorithm, dense symmetric n x n per knot
+ * replaces crba<T,USE_COMPRESSED_MEM> (algorithms/_crba.py:310-375; kernel :254-308); only q (the first n
+ * elements of each knot's row) is read */
+int grid_crba_f32(const float *d_q, int stride, float *d_M, int num_knots, void *stream);
+int grid_crba_f64(const double *d_q, int stride, double *d_M, int num_knots, void *stream);
 
 /* ---- host-buffer entry points (the reference's default host semantics: H2D, kernel, D2H, blocking;
  * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / n out). */

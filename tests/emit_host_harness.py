@@ -19,7 +19,19 @@ PRELUDE = """
 #define __restrict__
 #define GRID_FENCE() do { } while (0)
 #define GRID_SYNC() do { } while (0)
-namespace grid_rt { static inline void grid_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); } }
+namespace grid_rt {
+static inline void grid_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); }
+struct double_pair { double x, y; };
+template <typename T> using pair_t = double_pair;
+template <typename T> static inline double_pair mkp(T a, T b) { double_pair r; r.x = a; r.y = b; return r; }
+template <typename T> static inline double_pair pbc(T s) { return mkp<T>(s, s); }
+static inline double_pair pfma(double_pair a, double s, double_pair c) { return mkp<double>(a.x * s + c.x, a.y * s + c.y); }
+static inline double_pair pmul(double_pair a, double s) { return mkp<double>(a.x * s, a.y * s); }
+static inline double_pair padd(double_pair a, double_pair b) { return mkp<double>(a.x + b.x, a.y + b.y); }
+static inline double_pair psub(double_pair a, double_pair b) { return mkp<double>(a.x - b.x, a.y - b.y); }
+static inline double_pair padds(double_pair a, double s) { return mkp<double>(a.x + s, a.y + s); }
+static inline double_pair pneg(double_pair a) { return mkp<double>(-a.x, -a.y); }
+}
 """
 
 
