@@ -87,7 +87,7 @@ class GRiDCodeGenerator:
 
     def _temp_mem_size(self, key: str) -> int:
         """Per-knot state elements (the reference's s_temp size plays this role)."""
-        return max(self._body(v).nslots for v in self._variants(key))
+        return max([self._body(v).nslots for v in self._variants(key)] or [0])
 
     # ------------------------------------------------------ generic tiers
     def _gen_inner(self, key: str, variants: Optional[List[str]] = None):
@@ -115,11 +115,18 @@ class GRiDCodeGenerator:
     def _gen_algo(self, key: str):
         """inner -> device/kernel -> launcher -> host x3, like the reference's gen_<algo> drivers
         (e.g. algorithms/_inverse_dynamics.py:514-533)."""
+        if not self._variants(key):
+            return      # e.g. the second-order kernels of a robot above GRID_SECOND_ORDER_MAX_JOINTS
         self._gen_inner(key)
         self._gen_device(key)
         self._gen_kernel(key)
         for mode in (0, 1, 2):
             self._gen_host(key, mode)
+        if key == "idsva_so":   # the reference's banner calls this host function idsva_so_host (GRiDCodeGenerator.py:368)
+            self._add_block("template <typename T>\n__host__\nvoid idsva_so_host(gridData<T> *hd_data, const robotModel<T> "
+                            "*d_robotModel, const T gravity, const int num_timesteps,\n        const dim3 block_dimms, "
+                            "const dim3 thread_dimms, cudaStream_t *streams) {\n    idsva_so<T>(hd_data, d_robotModel, "
+                            "gravity, num_timesteps, block_dimms, thread_dimms, streams);\n}\n")
 
 
 def _bind(key: str):
@@ -150,7 +157,7 @@ def _bind(key: str):
 
 
 for _key in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-             "forward_dynamics_gradient", "aba", "crba"):
+             "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so"):
     _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner_temp_mem_size", _t)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner", _i)
@@ -173,7 +180,7 @@ GRiDCodeGenerator.gen_crba_device_temp_mem_size = GRiDCodeGenerator.gen_crba_inn
 from .emit import scaffold as _sc  # noqa: E402
 
 ALGO_ORDER = ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-              "forward_dynamics_gradient", "aba", "crba")
+              "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so")
 
 
 def gen_add_includes(self, use_thread_group=False):
@@ -214,7 +221,8 @@ def gen_add_constants_helpers(self):
              "const int KNOTS_PER_WARP = 32;    // one lane owns one knot point",
              "const int SUGGESTED_THREADS = 32; // single-warp CTAs: warps never synchronise with each other"]
     per4, per8 = _scratch_constants(self)
-    lines += [f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
+    lines += [f"#define GRID_HAS_SECOND_ORDER {int(_hdr.second_order_enabled(n))}",
+              f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F64 = {per8};",
               "const int GRID_SCRATCH_BLOCKS_PER_SM = 2;"]
     self.gen_add_code_lines(lines)
@@ -249,7 +257,7 @@ def gen_all_code(self, use_thread_group=False, include_base_inertia=False, inclu
              "    __host__   gridData<T> *hd_data = init_gridData<T,NUM_TIMESTEPS>();",
              "    __host__   close_grid<T>(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> *hd_data)",
              "  per ALGORITHM in {inverse_dynamics, direct_minv, forward_dynamics, inverse_dynamics_gradient,",
-             "                    forward_dynamics_gradient, aba, crba}:",
+             "                    forward_dynamics_gradient, aba, crba, idsva_so, fdsva_so}:",
              "    __device__ ALGORITHM_inner<T,NT>(T *o, const T *q, ..., T *S, const T gravity)   one thread = one knot point",
              "    __device__ ALGORITHM_device<T>(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) one warp = 32 knot points",
              "    __global__ ALGORITHM_kernel<T>(T *d_out, const T *d_in, const int stride, ..., const robotModel<T> *, const T gravity, const int NUM_TIMESTEPS)",
@@ -264,7 +272,8 @@ def gen_all_code(self, use_thread_group=False, include_base_inertia=False, inclu
     self.gen_add_code_line("namespace " + self.file_namespace + " {", True)
     self.gen_add_constants_helpers()
     for key in ALGO_ORDER:
-        getattr(self, "gen_" + key)(use_thread_group)
+        if self._variants(key):
+            getattr(self, "gen_" + key)(use_thread_group)
     self.gen_add_shared_mem_constants()
     self.gen_init_close_grid()
     self.gen_add_end_control_flow()

@@ -297,7 +297,14 @@ static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
     return want < cap ? want : cap;
 }
 
-// Number of CTAs the global state scratch attached to the robot model can serve (0 = none allocated).
-static int& scratch_blocks() { static int v = 0; return v; }
+// Number of CTAs the global state scratch attached to a robot model serves on the current device: a pure function
+// of the device (SM count x blocks_per_sm), so that init_robotModel (which allocates it) and every launcher agree
+// without sharing state across translation units.  Returns 0 on error.
+static int scratch_capacity(int blocks_per_sm) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    return sms * blocks_per_sm;
+}
 
 }  // namespace grid_rt

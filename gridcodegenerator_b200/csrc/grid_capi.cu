@@ -1,5 +1,11 @@
 // grid_capi.cu -- extern "C" surface (include/grid_b200.h) over one emitted grid.cuh.
-// Compiled once per robot:  nvcc -gencode arch=compute_100a,code=sm_100a -I<dir with grid.cuh> ...
+// Compiled per robot:  nvcc -gencode arch=compute_100a,code=sm_100a -I<dir with grid.cuh> ...
+//
+// The emitted kernels are large straight-line functions, so the build (runtime.build_library) compiles this file
+// several times in parallel, each time with -DGRID_PARTS=<bitmask of algorithms> -DGRID_DTYPES=<1 f32 | 2 f64>,
+// and links the objects into one libgrid_<robot>.so.  Compiled without those macros it is the whole library in
+// one translation unit.  Shared state (robot-model handles, host workspace, last error) is defined by the part
+// that has PART_CORE and dtype f32, and is referenced by the others through hidden-visibility symbols.
 #include "grid.cuh"
 #include "grid_b200.h"
 
@@ -9,22 +15,24 @@
 #ifndef GRID_ROBOT_NAME
 #define GRID_ROBOT_NAME "robot"
 #endif
-
-namespace {
-
-thread_local std::string g_last_error;
-
-int fail(cudaError_t e, const char* where) {
-    if (e == cudaSuccess) return 0;
-    g_last_error = std::string(where) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
-    return static_cast<int>(e);
-}
-int bad_arg(const char* where, const char* what) {
-    g_last_error = std::string(where) + ": " + what;
-    return static_cast<int>(cudaErrorInvalidValue);
-}
+#define PART_CORE 0x01       // introspection, release, shared state, ID, MINV, FD
+#define PART_ID_DU 0x02
+#define PART_FD_DU 0x04
+#define PART_FD_DU_QM 0x08
+#define PART_ABA_CRBA 0x10
+#define PART_IDSVA 0x20
+#define PART_FDSVA 0x40
+#ifndef GRID_PARTS
+#define GRID_PARTS 0xFF
+#endif
+#ifndef GRID_DTYPES
+#define GRID_DTYPES 3
+#endif
+#define HAS(p) ((GRID_PARTS & (p)) != 0)
+#define HIDDEN __attribute__((visibility("hidden")))
 
 constexpr int MAX_DEVICES = 16;
+constexpr int N = grid::NUM_JOINTS;
 
 // robot model handle (owns the optional global state scratch) per device and scalar type
 template <typename T>
@@ -51,15 +59,12 @@ struct Models {
         cudaSetDevice(cur);
     }
 };
-template <typename T>
-Models<T>& models() { static Models<T> m; return m; }
 
 // cached device workspace + streams of the host-buffer entry points (current device only)
 struct HostWork {
     void* d_in = nullptr; void* d_in2 = nullptr; void* d_out = nullptr;
     size_t in_bytes = 0, in2_bytes = 0, out_bytes = 0;
     cudaStream_t streams[3] = {};
-    cudaEvent_t ev[3] = {};
     bool have_streams = false;
     int device = -1;
     std::mutex mu;
@@ -69,10 +74,8 @@ struct HostWork {
         if (e != cudaSuccess) return e;
         if (dev != device) { free_all(); device = dev; }
         if (!have_streams) {
-            for (int i = 0; i < 3; i++) {
+            for (int i = 0; i < 3; i++)
                 if ((e = cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
-                if ((e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming)) != cudaSuccess) return e;
-            }
             have_streams = true;
         }
         if ((e = grow(&d_in, &in_bytes, in_b)) != cudaSuccess) return e;
@@ -92,87 +95,44 @@ struct HostWork {
         if (d_in2) cudaFree(d_in2);
         if (d_out) cudaFree(d_out);
         d_in = d_in2 = d_out = nullptr; in_bytes = in2_bytes = out_bytes = 0;
-        if (have_streams) for (int i = 0; i < 3; i++) { cudaStreamDestroy(streams[i]); cudaEventDestroy(ev[i]); }
+        if (have_streams) for (int i = 0; i < 3; i++) cudaStreamDestroy(streams[i]);
         have_streams = false;
     }
 };
-HostWork& host_work() { static HostWork w; return w; }
 
-constexpr int N = grid::NUM_JOINTS;
+// ---- state shared by all parts of one library (hidden: not visible to other libgrid_<robot>.so files)
+HIDDEN extern Models<float> grid_capi_models_f32;
+HIDDEN extern Models<double> grid_capi_models_f64;
+HIDDEN extern HostWork grid_capi_host_work;
+HIDDEN std::string& grid_capi_last_error();
+#if HAS(PART_CORE) && (GRID_DTYPES & 1)
+Models<float> grid_capi_models_f32;
+Models<double> grid_capi_models_f64;
+HostWork grid_capi_host_work;
+std::string& grid_capi_last_error() { static thread_local std::string s; return s; }
+#endif
 
-// ---- device-pointer implementations
-template <typename T>
-int inverse_dynamics_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_c, int nk, T g, void* s) {
-    const char* fn = "grid_inverse_dynamics";
-    if (nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_c))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    cudaStream_t st = static_cast<cudaStream_t>(s);
-    return fail(d_qdd ? grid::inverse_dynamics_qdd_launch<T>(d_c, d_q_qd, stride, d_qdd, m, g, nk, st)
-                      : grid::inverse_dynamics_launch<T>(d_c, d_q_qd, stride, m, g, nk, st), fn);
-}
-template <typename T>
-int direct_minv_impl(const T* d_q, int stride, T* d_Minv, int nk, void* s) {
-    const char* fn = "grid_direct_minv";
-    if (nk < 0 || stride < N || (nk > 0 && (!d_q || !d_Minv))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::direct_minv_launch<T>(d_Minv, d_q, stride, m, nk, static_cast<cudaStream_t>(s)), fn);
-}
-template <typename T>
-int forward_dynamics_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
-    const char* fn = "grid_forward_dynamics";
-    if (nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::forward_dynamics_launch<T>(d_qdd, d_in, stride, m, g, nk, static_cast<cudaStream_t>(s)), fn);
-}
-template <typename T>
-int inverse_dynamics_gradient_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_out, int nk, T g, void* s) {
-    const char* fn = "grid_inverse_dynamics_gradient";
-    if (nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_out))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    cudaStream_t st = static_cast<cudaStream_t>(s);
-    return fail(d_qdd ? grid::inverse_dynamics_gradient_qdd_launch<T>(d_out, d_q_qd, stride, d_qdd, m, g, nk, st)
-                      : grid::inverse_dynamics_gradient_launch<T>(d_out, d_q_qd, stride, m, g, nk, st), fn);
-}
-template <typename T>
-int forward_dynamics_gradient_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {
-    const char* fn = "grid_forward_dynamics_gradient";
-    if (nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::forward_dynamics_gradient_launch<T>(d_out, d_in, stride, m, g, nk, static_cast<cudaStream_t>(s)), fn);
-}
-template <typename T>
-int forward_dynamics_gradient_qdd_minv_impl(const T* d_q_qd, int stride, const T* d_qdd, const T* d_Minv, T* d_out,
-                                            int nk, T g, void* s) {
-    const char* fn = "grid_forward_dynamics_gradient_qdd_minv";
-    if (nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_qdd || !d_Minv || !d_out)))
-        return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::forward_dynamics_gradient_qdd_minv_launch<T>(d_out, d_q_qd, stride, d_qdd, d_Minv, m, g, nk,
-                                                                   static_cast<cudaStream_t>(s)), fn);
-}
+namespace {
 
-template <typename T>
-int aba_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
-    const char* fn = "grid_aba";
-    if (nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::aba_launch<T>(d_qdd, d_in, stride, m, g, nk, static_cast<cudaStream_t>(s)), fn);
+template <typename T> Models<T>& models();
+template <> Models<float>& models<float>() { return grid_capi_models_f32; }
+template <> Models<double>& models<double>() { return grid_capi_models_f64; }
+
+int fail(cudaError_t e, const char* where) {
+    if (e == cudaSuccess) return 0;
+    grid_capi_last_error() = std::string(where) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return static_cast<int>(e);
 }
-template <typename T>
-int crba_impl(const T* d_q, int stride, T* d_M, int nk, void* s) {
-    const char* fn = "grid_crba";
-    if (nk < 0 || stride < N || (nk > 0 && (!d_q || !d_M))) return bad_arg(fn, "bad pointer / stride / num_knots");
-    auto* m = models<T>().get();
-    if (!m) return bad_arg(fn, "no CUDA device");
-    return fail(grid::crba_launch<T>(d_M, d_q, stride, m, T(0), nk, static_cast<cudaStream_t>(s)), fn);
+int bad_arg(const char* where, const char* what) {
+    grid_capi_last_error() = std::string(where) + ": " + what;
+    return static_cast<int>(cudaErrorInvalidValue);
 }
+#define GRID_CHECK_ARGS(FN, COND)                                                       \
+    const char* fn = FN;                                                                \
+    if (COND) return bad_arg(fn, "bad pointer / stride / num_knots");                   \
+    auto* m = models<T>().get();                                                        \
+    if (!m) return bad_arg(fn, "no CUDA device");                                       \
+    cudaStream_t st = static_cast<cudaStream_t>(s); (void)st
 
 // ---- host-buffer pipeline: chunks of the batch rotate over three streams so that the H2D copy of
 // chunk i+1, the kernel of chunk i and the D2H copy of chunk i-1 overlap (PCIe is full duplex).
@@ -180,7 +140,7 @@ template <typename T, class Launch>
 int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int out_per_knot, int nk, Launch launch) {
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
-    HostWork& w = host_work();
+    HostWork& w = grid_capi_host_work;
     std::lock_guard<std::mutex> lk(w.mu);
     cudaError_t e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), 0, size_t(nk) * out_per_knot * sizeof(T));
     if (e != cudaSuccess) return fail(e, fn);
@@ -205,10 +165,8 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
     return 0;
 }
 
-}  // namespace
-
-#define GRID_INFO_CASE(IDX, CFG, ALGO, KPTR)                                                                      \
-    case IDX: {                                                                                                   \
+#define GRID_INFO(CFG, ALGO, KPTR)                                                                                \
+    {                                                                                                             \
         if (what == 0) return long(grid::CFG<T>::SMEM_BYTES);                                                     \
         if (what == 1) return long(grid::CFG<T>::NT);                                                             \
         if (what == 2) return long(grid::ALGO<T>::SLOTS);                                                         \
@@ -219,69 +177,88 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
         return -1;                                                                                                \
     }
 
+}  // namespace
+
+// ---- per-part kernel introspection, dispatched from grid_kernel_info (defined in the core f32 part)
+#define DECL_INFO(NAME) HIDDEN long grid_capi_info_##NAME##_f32(int algo, int what); \
+                        HIDDEN long grid_capi_info_##NAME##_f64(int algo, int what);
+DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(aba_crba) DECL_INFO(idsva) DECL_INFO(fdsva)
+
+// Everything below is instantiated for the dtypes of this translation unit through GRID_FOR_DTYPES(X):
+#if (GRID_DTYPES & 1) && (GRID_DTYPES & 2)
+#define GRID_FOR_DTYPES(X) X(f32, float) X(f64, double)
+#elif (GRID_DTYPES & 1)
+#define GRID_FOR_DTYPES(X) X(f32, float)
+#else
+#define GRID_FOR_DTYPES(X) X(f64, double)
+#endif
+
+// =============================================================== core: ID, MINV, FD
+#if HAS(PART_CORE)
+namespace {
 template <typename T>
-long kernel_info(int algo, int what) {
+int inverse_dynamics_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_c, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_inverse_dynamics", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_c)));
+    return fail(d_qdd ? grid::inverse_dynamics_qdd_launch<T>(d_c, d_q_qd, stride, d_qdd, m, g, nk, st)
+                      : grid::inverse_dynamics_launch<T>(d_c, d_q_qd, stride, m, g, nk, st), fn);
+}
+template <typename T>
+int direct_minv_impl(const T* d_q, int stride, T* d_Minv, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_direct_minv", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_Minv)));
+    return fail(grid::direct_minv_launch<T>(d_Minv, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+int forward_dynamics_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_forward_dynamics", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)));
+    return fail(grid::forward_dynamics_launch<T>(d_qdd, d_in, stride, m, g, nk, st), fn);
+}
+template <typename T>
+long info_core(int algo, int what) {
     using namespace grid;
     using RM = const robotModel<T>*;
     switch (algo) {
-        GRID_INFO_CASE(0, inverse_dynamics_cfg, inverse_dynamics_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(inverse_dynamics_kernel<T>))
-        GRID_INFO_CASE(1, inverse_dynamics_qdd_cfg, inverse_dynamics_qdd_algo,
-                       static_cast<void (*)(T*, const T*, const int, const T*, RM, const T, const int)>(inverse_dynamics_kernel<T>))
-        GRID_INFO_CASE(2, direct_minv_cfg, direct_minv_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const int)>(direct_minv_kernel<T>))
-        GRID_INFO_CASE(3, forward_dynamics_cfg, forward_dynamics_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_kernel<T>))
-        GRID_INFO_CASE(4, inverse_dynamics_gradient_cfg, inverse_dynamics_gradient_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(inverse_dynamics_gradient_kernel<T>))
-        GRID_INFO_CASE(5, inverse_dynamics_gradient_qdd_cfg, inverse_dynamics_gradient_qdd_algo,
-                       static_cast<void (*)(T*, const T*, const int, const T*, RM, const T, const int)>(inverse_dynamics_gradient_kernel<T>))
-        GRID_INFO_CASE(6, forward_dynamics_gradient_cfg, forward_dynamics_gradient_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
-        GRID_INFO_CASE(7, forward_dynamics_gradient_qdd_minv_cfg, forward_dynamics_gradient_qdd_minv_algo,
-                       static_cast<void (*)(T*, const T*, const int, const T*, const T*, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
-        GRID_INFO_CASE(8, aba_cfg, aba_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(aba_kernel<T>))
-        GRID_INFO_CASE(9, crba_cfg, crba_algo,
-                       static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(crba_kernel<T>))
+        case 0: GRID_INFO(inverse_dynamics_cfg, inverse_dynamics_algo,
+                          static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(inverse_dynamics_kernel<T>))
+        case 1: GRID_INFO(inverse_dynamics_qdd_cfg, inverse_dynamics_qdd_algo,
+                          static_cast<void (*)(T*, const T*, const int, const T*, RM, const T, const int)>(inverse_dynamics_kernel<T>))
+        case 2: GRID_INFO(direct_minv_cfg, direct_minv_algo,
+                          static_cast<void (*)(T*, const T*, const int, RM, const int)>(direct_minv_kernel<T>))
+        case 3: GRID_INFO(forward_dynamics_cfg, forward_dynamics_algo,
+                          static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_kernel<T>))
     }
     return -1;
 }
-extern "C" {
+}  // namespace
+#define X_CORE(SUF, T)                                                                                             \
+    long grid_capi_info_core_##SUF(int algo, int what) { return info_core<T>(algo, what); }                        \
+    extern "C" int grid_inverse_dynamics_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) {      \
+        return inverse_dynamics_impl<T>(a, st, b, o, nk, g, s); }                                                  \
+    extern "C" int grid_direct_minv_##SUF(const T* a, int st, T* o, int nk, void* s) {                             \
+        return direct_minv_impl<T>(a, st, o, nk, s); }                                                             \
+    extern "C" int grid_forward_dynamics_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {                   \
+        return forward_dynamics_impl<T>(a, st, o, nk, g, s); }
+GRID_FOR_DTYPES(X_CORE)
 
+#if (GRID_DTYPES & 1)
+extern "C" {
 int grid_num_joints(void) { return N; }
 const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
-const char* grid_last_error(void) { return g_last_error.c_str(); }
-int grid_abi_version(void) { return 1; }
-
+const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
+int grid_abi_version(void) { return 3; }
+int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
 long grid_kernel_info(int algo, int is_f64, int what) {
-    return is_f64 ? kernel_info<double>(algo, what) : kernel_info<float>(algo, what);
+#define DISPATCH(NAME) return is_f64 ? grid_capi_info_##NAME##_f64(algo, what) : grid_capi_info_##NAME##_f32(algo, what);
+    switch (algo) {
+        case 0: case 1: case 2: case 3: DISPATCH(core)
+        case 4: case 5: DISPATCH(id_du)
+        case 6: DISPATCH(fd_du)
+        case 7: DISPATCH(fd_du_qm)
+        case 8: case 9: DISPATCH(aba_crba)
+        case 10: DISPATCH(idsva)
+        case 11: DISPATCH(fdsva)
+    }
+    return -1;
 }
-
-#define GRID_DEFINE(SUF, T)                                                                                        \
-    int grid_inverse_dynamics_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) {                 \
-        return inverse_dynamics_impl<T>(a, st, b, o, nk, g, s); }                                                  \
-    int grid_direct_minv_##SUF(const T* a, int st, T* o, int nk, void* s) {                                        \
-        return direct_minv_impl<T>(a, st, o, nk, s); }                                                             \
-    int grid_forward_dynamics_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {                              \
-        return forward_dynamics_impl<T>(a, st, o, nk, g, s); }                                                     \
-    int grid_inverse_dynamics_gradient_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) {        \
-        return inverse_dynamics_gradient_impl<T>(a, st, b, o, nk, g, s); }                                         \
-    int grid_forward_dynamics_gradient_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {                     \
-        return forward_dynamics_gradient_impl<T>(a, st, o, nk, g, s); }                                            \
-    int grid_forward_dynamics_gradient_qdd_minv_##SUF(const T* a, int st, const T* b, const T* c, T* o, int nk,   \
-                                                      T g, void* s) {                                              \
-        return forward_dynamics_gradient_qdd_minv_impl<T>(a, st, b, c, o, nk, g, s); }                             \
-    int grid_aba_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return aba_impl<T>(a, st, o, nk, g, s); }  \
-    int grid_crba_##SUF(const T* a, int st, T* o, int nk, void* s) { return crba_impl<T>(a, st, o, nk, s); }      \
-    int grid_forward_dynamics_gradient_host_##SUF(const T* h_in, T* h_out, int nk, T g) {                          \
-        return host_pipeline<T>("grid_forward_dynamics_gradient_host", h_in, 3 * N, h_out, 2 * N * N, nk,          \
-            [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
-                return forward_dynamics_gradient_impl<T>(di, 3 * N, dout, c, g, st); }); }
-
-GRID_DEFINE(f32, float)
-GRID_DEFINE(f64, double)
-
 int grid_forward_dynamics_host_f32(const float* h_in, float* h_out, int nk, float g) {
     return host_pipeline<float>("grid_forward_dynamics_host", h_in, 3 * N, h_out, N, nk,
         [g](const float* di, float* dout, int c, cudaStream_t st) {
@@ -292,7 +269,7 @@ int grid_inverse_dynamics_host_f32(const float* h_in, float* h_out, int nk, floa
     const char* fn = "grid_inverse_dynamics_host";
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
-    HostWork& w = host_work();
+    HostWork& w = grid_capi_host_work;
     std::lock_guard<std::mutex> lk(w.mu);
     cudaError_t e = w.ensure(size_t(nk) * 3 * N * sizeof(float), size_t(nk) * N * sizeof(float), size_t(nk) * N * sizeof(float));
     if (e != cudaSuccess) return fail(e, fn);
@@ -308,12 +285,170 @@ int grid_inverse_dynamics_host_f32(const float* h_in, float* h_out, int nk, floa
     if ((e = cudaMemcpyAsync(h_out, d_out, size_t(nk) * N * sizeof(float), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return fail(e, fn);
     return fail(cudaStreamSynchronize(st), fn);
 }
-
 int grid_release(void) {
-    host_work().free_all();
-    models<float>().release();
-    models<double>().release();
+    grid_capi_host_work.free_all();
+    grid_capi_models_f32.release();
+    grid_capi_models_f64.release();
     return 0;
 }
-
 }  // extern "C"
+#endif
+#endif  // PART_CORE
+
+// =============================================================== grad ID
+#if HAS(PART_ID_DU)
+namespace {
+template <typename T>
+int inverse_dynamics_gradient_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_out, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_inverse_dynamics_gradient", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_out)));
+    return fail(d_qdd ? grid::inverse_dynamics_gradient_qdd_launch<T>(d_out, d_q_qd, stride, d_qdd, m, g, nk, st)
+                      : grid::inverse_dynamics_gradient_launch<T>(d_out, d_q_qd, stride, m, g, nk, st), fn);
+}
+template <typename T>
+long info_id_du(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    switch (algo) {
+        case 4: GRID_INFO(inverse_dynamics_gradient_cfg, inverse_dynamics_gradient_algo,
+                          static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(inverse_dynamics_gradient_kernel<T>))
+        case 5: GRID_INFO(inverse_dynamics_gradient_qdd_cfg, inverse_dynamics_gradient_qdd_algo,
+                          static_cast<void (*)(T*, const T*, const int, const T*, RM, const T, const int)>(inverse_dynamics_gradient_kernel<T>))
+    }
+    return -1;
+}
+}  // namespace
+#define X_ID_DU(SUF, T)                                                                                            \
+    long grid_capi_info_id_du_##SUF(int algo, int what) { return info_id_du<T>(algo, what); }                      \
+    extern "C" int grid_inverse_dynamics_gradient_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) { \
+        return inverse_dynamics_gradient_impl<T>(a, st, b, o, nk, g, s); }
+GRID_FOR_DTYPES(X_ID_DU)
+#endif
+
+// =============================================================== grad FD (the metric kernel)
+#if HAS(PART_FD_DU)
+namespace {
+template <typename T>
+int forward_dynamics_gradient_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_forward_dynamics_gradient", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));
+    return fail(grid::forward_dynamics_gradient_launch<T>(d_out, d_in, stride, m, g, nk, st), fn);
+}
+template <typename T>
+long info_fd_du(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    if (algo == 6) GRID_INFO(forward_dynamics_gradient_cfg, forward_dynamics_gradient_algo,
+                             static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
+    return -1;
+}
+}  // namespace
+#define X_FD_DU(SUF, T)                                                                                            \
+    long grid_capi_info_fd_du_##SUF(int algo, int what) { return info_fd_du<T>(algo, what); }                      \
+    extern "C" int grid_forward_dynamics_gradient_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {          \
+        return forward_dynamics_gradient_impl<T>(a, st, o, nk, g, s); }                                            \
+    extern "C" int grid_forward_dynamics_gradient_host_##SUF(const T* h_in, T* h_out, int nk, T g) {               \
+        return host_pipeline<T>("grid_forward_dynamics_gradient_host", h_in, 3 * N, h_out, 2 * N * N, nk,          \
+            [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
+                return forward_dynamics_gradient_impl<T>(di, 3 * N, dout, c, g, st); }); }
+GRID_FOR_DTYPES(X_FD_DU)
+#endif
+
+#if HAS(PART_FD_DU_QM)
+namespace {
+template <typename T>
+int forward_dynamics_gradient_qdd_minv_impl(const T* d_q_qd, int stride, const T* d_qdd, const T* d_Minv, T* d_out,
+                                            int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_forward_dynamics_gradient_qdd_minv",
+                    nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_qdd || !d_Minv || !d_out)));
+    return fail(grid::forward_dynamics_gradient_qdd_minv_launch<T>(d_out, d_q_qd, stride, d_qdd, d_Minv, m, g, nk, st), fn);
+}
+template <typename T>
+long info_fd_du_qm(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    if (algo == 7) GRID_INFO(forward_dynamics_gradient_qdd_minv_cfg, forward_dynamics_gradient_qdd_minv_algo,
+                             static_cast<void (*)(T*, const T*, const int, const T*, const T*, RM, const T, const int)>(forward_dynamics_gradient_kernel<T>))
+    return -1;
+}
+}  // namespace
+#define X_FD_DU_QM(SUF, T)                                                                                         \
+    long grid_capi_info_fd_du_qm_##SUF(int algo, int what) { return info_fd_du_qm<T>(algo, what); }                \
+    extern "C" int grid_forward_dynamics_gradient_qdd_minv_##SUF(const T* a, int st, const T* b, const T* c, T* o, \
+                                                                 int nk, T g, void* s) {                           \
+        return forward_dynamics_gradient_qdd_minv_impl<T>(a, st, b, c, o, nk, g, s); }
+GRID_FOR_DTYPES(X_FD_DU_QM)
+#endif
+
+// =============================================================== ABA, CRBA
+#if HAS(PART_ABA_CRBA)
+namespace {
+template <typename T>
+int aba_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_aba", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)));
+    return fail(grid::aba_launch<T>(d_qdd, d_in, stride, m, g, nk, st), fn);
+}
+template <typename T>
+int crba_impl(const T* d_q, int stride, T* d_M, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_crba", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_M)));
+    return fail(grid::crba_launch<T>(d_M, d_q, stride, m, T(0), nk, st), fn);
+}
+template <typename T>
+long info_aba_crba(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    switch (algo) {
+        case 8: GRID_INFO(aba_cfg, aba_algo, static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(aba_kernel<T>))
+        case 9: GRID_INFO(crba_cfg, crba_algo, static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(crba_kernel<T>))
+    }
+    return -1;
+}
+}  // namespace
+#define X_ABA_CRBA(SUF, T)                                                                                         \
+    long grid_capi_info_aba_crba_##SUF(int algo, int what) { return info_aba_crba<T>(algo, what); }                \
+    extern "C" int grid_aba_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return aba_impl<T>(a, st, o, nk, g, s); } \
+    extern "C" int grid_crba_##SUF(const T* a, int st, T* o, int nk, void* s) { return crba_impl<T>(a, st, o, nk, s); }
+GRID_FOR_DTYPES(X_ABA_CRBA)
+#endif
+
+// =============================================================== second order (robots up to 8 joints)
+#define X_SO(NAME, LAUNCH, CFG, ALGO, KERNEL, IDX)                                                                 \
+    namespace {                                                                                                    \
+    template <typename T> int NAME##_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {            \
+        GRID_CHECK_ARGS("grid_" #NAME, nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));                 \
+        return fail(grid::LAUNCH<T>(d_out, d_in, stride, m, g, nk, st), fn);                                       \
+    }                                                                                                              \
+    template <typename T> long info_##NAME(int algo, int what) {                                                   \
+        using namespace grid;                                                                                      \
+        using RM = const robotModel<T>*;                                                                           \
+        if (algo == IDX) GRID_INFO(CFG, ALGO, static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(KERNEL<T>)) \
+        return -1;                                                                                                 \
+    }                                                                                                              \
+    }
+#define X_SO_STUB(NAME, SUF, T)                                                                                    \
+    long grid_capi_info_##NAME##_##SUF(int, int) { return -1; }                                                    \
+    extern "C" int grid_##NAME##_so_##SUF(const T*, int, T*, int, T, void*) {                                      \
+        grid_capi_last_error() = "grid_" #NAME "_so: this library was built without second-order kernels";         \
+        return static_cast<int>(cudaErrorNotSupported); }
+
+#if HAS(PART_IDSVA)
+#if GRID_HAS_SECOND_ORDER
+X_SO(idsva_so, idsva_so_launch, idsva_so_cfg, idsva_so_algo, idsva_so_kernel, 10)
+#define X_IDSVA(SUF, T)                                                                                            \
+    long grid_capi_info_idsva_##SUF(int algo, int what) { return info_idsva_so<T>(algo, what); }                   \
+    extern "C" int grid_idsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return idsva_so_impl<T>(a, st, o, nk, g, s); }
+#else
+#define X_IDSVA(SUF, T) X_SO_STUB(idsva, SUF, T)
+#endif
+GRID_FOR_DTYPES(X_IDSVA)
+#endif
+
+#if HAS(PART_FDSVA)
+#if GRID_HAS_SECOND_ORDER
+X_SO(fdsva_so, fdsva_so_launch, fdsva_so_cfg, fdsva_so_algo, fdsva_so_kernel, 11)
+#define X_FDSVA(SUF, T)                                                                                            \
+    long grid_capi_info_fdsva_##SUF(int algo, int what) { return info_fdsva_so<T>(algo, what); }                   \
+    extern "C" int grid_fdsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return fdsva_so_impl<T>(a, st, o, nk, g, s); }
+#else
+#define X_FDSVA(SUF, T) X_SO_STUB(fdsva, SUF, T)
+#endif
+GRID_FOR_DTYPES(X_FDSVA)
+#endif

@@ -53,19 +53,31 @@ class Ctx:
     def read_vec(self, ptr: str, prefix: str) -> List[V]:
         return [self.em.named(f"{prefix}{j}", f"{ptr}[{j}]") for j in range(self.n)]
 
-    def prologue(self, q_ptr: str = "q"):
+    def prologue(self, q_ptr: str = "q", seeded: bool = False):
         """sin/cos of every revolute joint angle (reference helpers/_topology_helpers.py:194-195) and the
-        factored transform handles."""
+        factored transform handles.  With `seeded`, q_j is AD seed j: sin/cos (or q for prismatic joints) carry
+        their first and second derivatives with respect to q_j (used when Em.ad_order > 0)."""
         em = self.em
         self.q = self.read_vec(q_ptr, "q_")
         self.X = []
         for j, jd in enumerate(self.m.joints):
             if jd.revolute:
                 em.line(f"T sn{j}, cs{j}; grid_sincos(q_{j}, &sn{j}, &cs{j});")
-                tr = Trig(V(s=f"sn{j}"), V(s=f"cs{j}"), self.q[j])
+                sn, cs = V(s=f"sn{j}"), V(s=f"cs{j}")
+                if seeded:
+                    nsn, ncs = em.tmp(f"-sn{j}"), em.tmp(f"-cs{j}")
+                    sn.d = {j: V(s=cs.s, d={j: V(s=nsn.s)})}
+                    cs.d = {j: V(s=nsn.s, d={j: V(s=ncs.s)})}
+                tr = Trig(sn, cs, self.q[j])
             else:
+                if seeded:
+                    self.q[j] = V(s=self.q[j].s, d={j: ONE})
                 tr = Trig(None, None, self.q[j])
             self.X.append(Xform(jd, tr))
+
+    def seed_vec(self, vec: Sequence[V], first_seed: int) -> List[V]:
+        """Mark vec[j] as AD seed first_seed + j."""
+        return [V(s=v.s, d={first_seed + j: ONE}) for j, v in enumerate(vec)]
 
 
 class Pusher:
@@ -674,15 +686,13 @@ def body_aba(model: Model) -> Body:
 
 
 # ===================================================================== CRBA
-def body_crba(model: Model) -> Body:
+def crba_matrix(cx: Ctx) -> Dict[tuple, V]:
     """Joint-space inertia matrix M(q), full symmetric, column-major (reference algorithms/_crba.py:30-209;
     Featherstone RBDA table 6.2).  The composite inertia of joint j is final once all its descendants (ids > j,
     DFS pre-order) have been folded in, so column j of M is produced right there by walking f_h = IC_j S up the
     ancestor chain; composite inertias live in their own storage (the reference accumulates them into the shared
     I table, _crba.py:81-143, and hard-codes n = 7 offsets)."""
-    cx = Ctx(model)
-    em, m, n = cx.em, model, model.n
-    cx.prologue()
+    em, m, n = cx.em, cx.m, cx.n
     carry: Dict[int, List[List[V]]] = {}
     in_state: Dict[int, bool] = {}
     Mv: Dict[tuple, V] = {}
@@ -722,7 +732,144 @@ def body_crba(model: Model) -> Body:
                         XtIX[r][k] = XtIX[k][r]
             _sym_store(em, "IC", p, XtIX)
             in_state[p] = True
+    return Mv
+
+
+def body_crba(model: Model) -> Body:
+    cx = Ctx(model)
+    em, n = cx.em, model.n
+    cx.prologue()
+    Mv = crba_matrix(cx)
     for col in range(n):
         for r in range(n):
             _out(em, col * n + r, Mv.get((min(r, col), max(r, col)), ZERO))
     return Body("crba_inner", "", cx, "M(q), dense symmetric, column-major")
+
+
+# ============================================================ second order
+def _d1(v: V, k: int) -> V:
+    return v.d[k] if (v.d and k in v.d) else ZERO
+
+
+def _d2(v: V, k: int, l: int) -> V:
+    """d2 v / d seed_k d seed_l (tangents are stored for l <= k only)."""
+    if l > k:
+        k, l = l, k
+    return _d1(_d1(v, k), l)
+
+
+def rnea_second_order(cx: Ctx, qd_in: Sequence[V], qdd: Sequence[V]):
+    """c = RNEA(q, qd, qdd) differentiated twice at emit time (forward-mode tangents through the same straight-line
+    RNEA as the first-order kernels) with seeds q_k -> k and qd_k -> n + k, qdd held fixed.  Returns c (n V's whose
+    .d / .d.d hold dc/du and d2c/du2).  Stands in for the reference's hand-derived IDSVA recursion
+    (algorithms/_idsva_so.py:167-912): same tensors, derived mechanically from the pinned RNEA."""
+    em, n = cx.em, cx.n
+    save = em.ad_order
+    em.ad_order = 2
+    qd = cx.seed_vec(qd_in, n)
+    rnea_forward(cx, qd, qdd, keep=False, fname="f2")
+    c = rnea_backward(cx, qd, keep_f=False, fname="f2")
+    em.ad_order = save
+    return c
+
+
+def mass_matrix_gradient(cx: Ctx) -> Dict[tuple, V]:
+    """M(q) by CRBA with first-order tangents: Mv[(i, j)].d[k] = dM_ij/dq_k, i <= j
+    (reference output dM_dq, algorithms/_idsva_so.py:159)."""
+    em = cx.em
+    save = em.ad_order
+    em.ad_order = 1
+    Mv = crba_matrix(cx)
+    em.ad_order = save
+    return Mv
+
+
+def _second_order_ctx(model: Model) -> Ctx:
+    cx = Ctx(model)
+    cx.em.regs_only = True      # tangents ride on the SSA values; the compiler places them (registers / local memory)
+    cx.em.fences = False
+    cx.prologue(seeded=True)
+    return cx
+
+
+def body_idsva_so(model: Model) -> Body:
+    """Second-order inverse-dynamics tensors (reference algorithms/_idsva_so.py; kernel :958-1028), 4 n^3 outputs:
+       out[0*n^3 + i*n^2 + j*n + k] = d2 tau_i / dq_j dq_k
+       out[1*n^3 + i*n^2 + j*n + k] = d2 tau_i / dqd_j dqd_k
+       out[2*n^3 + i*n^2 + j*n + k] = d2 tau_i / dqd_j dq_k
+       out[3*n^3 + i*n^2 + j*n + k] = d M_ij / dq_k
+    (tensor order of the reference: d2tau_dq2, d2tau_dqd2, d2tau_dvdq, dM_dq, _idsva_so.py:156-159)."""
+    cx = _second_order_ctx(model)
+    em, n = cx.em, model.n
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_")
+    c = rnea_second_order(cx, qd, qdd)
+    Mv = mass_matrix_gradient(cx)
+    n3 = n * n * n
+    for i in range(n):
+        for j in range(n):
+            for k in range(n):
+                idx = i * n * n + j * n + k
+                _out(em, idx, _d2(c[i], j, k))
+                _out(em, n3 + idx, _d2(c[i], n + j, n + k))
+                _out(em, 2 * n3 + idx, _d2(c[i], n + j, k))
+                _out(em, 3 * n3 + idx, _d1(Mv.get((min(i, j), max(i, j)), ZERO), k))
+    return Body("idsva_so_inner", "", cx, "second-order inverse dynamics tensors (4 n^3)")
+
+
+def body_fdsva_so(model: Model) -> Body:
+    """Second-order forward-dynamics tensors (reference algorithms/_fdsva_so.py:4-85; kernel :161-244), 4 n^3:
+       out[0*n^3 + i*n^2 + j*n + k] = d2 qdd_i / dq_j dq_k     = -Minv (T_qq[:,j,k] + dM_k A_q[:,j] + dM_j A_q[:,k])
+       out[1*n^3 + i*n^2 + j*n + k] = d2 qdd_i / dqd_j dqd_k   = -Minv  T_vv[:,j,k]
+       out[2*n^3 + i*n^2 + j*n + k] = d2 qdd_i / dqd_j dq_k    = -Minv (T_vq[:,j,k] + dM_k A_v[:,j])
+       out[3*n^3 + i*n^2 + j*n + k] = d2 qdd_i / dtau_j dq_k   = -Minv (dM_k Minv[:,j])
+    with T_* the IDSVA tensors at qdd = FD(q, qd, tau), dM_k = dM/dq_k, A_q = dqdd/dq, A_v = dqdd/dqd
+    (implicit differentiation of ID(q, qd, FD(q, qd, tau)) = tau; the reference's inner_dq / inner_cross /
+    inner_tau terms, _fdsva_so.py:52-83)."""
+    cx = _second_order_ctx(model)
+    em, n = cx.em, model.n
+    qd = cx.read_vec("qd", "qd_")
+    u = cx.read_vec("u", "u_")
+    em.comment("---- qdd = Minv (u - RNEA(q, qd, 0))")
+    rnea_forward(cx, qd, None, keep=False)
+    c0 = rnea_backward(cx, qd, keep_f=False)
+    articulated_inertias(cx)
+    Minv = minv_columns(cx)
+    qdd = fd_finish(cx, Minv, u, c0)
+    Mi = [[minv_get(Minv, r, k) for k in range(n)] for r in range(n)]
+    em.comment("---- RNEA(q, qd, qdd) with first and second order tangents")
+    c = rnea_second_order(cx, qd, qdd)
+    em.comment("---- dM/dq")
+    Mv = mass_matrix_gradient(cx)
+    dM = [[[_d1(Mv.get((min(i, L), max(i, L)), ZERO), k) for k in range(n)] for L in range(n)] for i in range(n)]
+    em.comment("---- first-order FD gradient A = -Minv dc/du")
+    Aq = [[em.lincomb([(-1.0, Mi[L][m_], _d1(c[m_], j)) for m_ in range(n)]) for j in range(n)] for L in range(n)]
+    Av = [[em.lincomb([(-1.0, Mi[L][m_], _d1(c[m_], n + j)) for m_ in range(n)]) for j in range(n)] for L in range(n)]
+    n3 = n * n * n
+    em.comment("---- d2qdd/dq2")
+    for j in range(n):
+        for k in range(j + 1):
+            inner = [em.lincomb([(1.0, dM[L][m_][k], Aq[m_][j]) for m_ in range(n)] +
+                                [(1.0, dM[L][m_][j], Aq[m_][k]) for m_ in range(n)], _d2(c[L], j, k)) for L in range(n)]
+            for i in range(n):
+                v = em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in range(n)])
+                _out(em, i * n * n + j * n + k, v)
+                if k != j:
+                    _out(em, i * n * n + k * n + j, v)
+    em.comment("---- d2qdd/dqd2")
+    for j in range(n):
+        for k in range(j + 1):
+            for i in range(n):
+                v = em.lincomb([(-1.0, Mi[i][L], _d2(c[L], n + j, n + k)) for L in range(n)])
+                _out(em, n3 + i * n * n + j * n + k, v)
+                if k != j:
+                    _out(em, n3 + i * n * n + k * n + j, v)
+    em.comment("---- d2qdd/dqd dq and d2qdd/dtau dq")
+    for j in range(n):
+        for k in range(n):
+            inner = [em.lincomb([(1.0, dM[L][m_][k], Av[m_][j]) for m_ in range(n)], _d2(c[L], n + j, k)) for L in range(n)]
+            inner_t = [em.lincomb([(1.0, dM[L][m_][k], Mi[m_][j]) for m_ in range(n)]) for L in range(n)]
+            for i in range(n):
+                _out(em, 2 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in range(n)]))
+                _out(em, 3 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner_t[L]) for L in range(n)]))
+    return Body("fdsva_so_inner", "", cx, "second-order forward dynamics tensors (4 n^3)")

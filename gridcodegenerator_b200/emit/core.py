@@ -21,12 +21,15 @@ class V:
     linear combinations of pairs with scalar coefficients become packed FFMA2 / FMUL2 / FADD2 on sm_100a).
     A scalar used where a pair is expected means the broadcast (s, s)."""
 
-    __slots__ = ("c", "s", "p")
+    __slots__ = ("c", "s", "p", "d")
 
-    def __init__(self, c: Optional[float] = None, s: Optional[str] = None, p: bool = False):
+    def __init__(self, c: Optional[float] = None, s: Optional[str] = None, p: bool = False, d=None):
         self.c = None if c is None else float(c)
         self.s = s
         self.p = p
+        # emit-time forward-mode AD (Em.ad_order > 0): d[seed] is the V holding d(self)/d(seed); those V's carry
+        # their own d (second order) for seeds <= seed.  None = no dependence on any seed.
+        self.d = d
 
     @property
     def is_const(self):
@@ -71,6 +74,10 @@ class Em:
         # small robots: "state" is plain SSA values (registers; ptxas spills the coldest to local memory = L1)
         self.regs_only = False
         self.reg_state: Dict[Tuple, V] = {}
+        # emit-time forward-mode AD: 0 = off, 1 = first-order tangents, 2 = also second order
+        self.ad_order = 0
+        self._ad_depth = 0
+        self._ad_cap = None
 
     # ------------------------------------------------------------------ text
     def line(self, txt: str):
@@ -124,8 +131,96 @@ class Em:
 
     # ------------------------------------------------------------ arithmetic
     def lincomb(self, terms: Sequence[Tuple], acc: Optional[V] = None) -> V:
-        """sum_k coef_k * x_k [* y_k] (+ acc).  terms: (coef, x) or (coef, x, y) with coef a Python
-        float and x, y V's.  Constants are folded; emits at most one statement."""
+        """sum_k coef_k * x_k [* y_k ...] (+ acc), with emit-time forward-mode differentiation: when ad_order > 0
+        and some factor carries tangents (V.d), the result carries the tangents given by the product rule, computed
+        by recursive calls (the tangent of a tangent gives the second order; only seed pairs l <= k are formed)."""
+        r = self._lincomb(terms, acc)
+        if self.ad_order <= self._ad_depth:
+            return r
+        seeds = set()
+        for t in terms:
+            for v in t[1:]:
+                if v is not None and v.d:
+                    seeds.update(v.d.keys())
+        if acc is not None and acc.d:
+            seeds.update(acc.d.keys())
+        if self._ad_cap is not None:
+            seeds = {k for k in seeds if k <= self._ad_cap}
+        if not seeds:
+            return r
+        r = V(c=r.c, s=r.s, p=r.p)          # fresh object: r may alias an input
+        r.d = {}
+        depth, cap = self._ad_depth, self._ad_cap
+        for k in sorted(seeds):
+            tt = []
+            for t in terms:
+                fs = [f for f in t[1:] if f is not None]
+                for i, f in enumerate(fs):
+                    fk = f.d.get(k) if f.d else None
+                    if fk is not None:
+                        tt.append((t[0], fk) + tuple(g for m_, g in enumerate(fs) if m_ != i))
+            ak = acc.d.get(k) if (acc is not None and acc.d) else None
+            self._ad_depth, self._ad_cap = depth + 1, k
+            rk = self.lincomb(tt, ak)
+            self._ad_depth, self._ad_cap = depth, cap
+            if not rk.is_zero():
+                r.d[k] = rk
+        if not r.d:
+            r.d = None
+        return r
+
+    def elem(self, expr: str, inputs: Sequence[V], partials: Sequence[V], second=None) -> V:
+        """A differentiable elementary function g(u_1..u_m) emitted as `expr`.  partials[a] = dg/du_a and
+        second[a][b] = d2g/du_a du_b are V's WITHOUT tangents (plain expressions of the inputs); the tangents of
+        the result follow from the chain rule:  r_k = sum_a g_a u_a,k ;
+        r_kl = sum_a g_a u_a,kl + sum_ab g_ab u_a,k u_b,l."""
+        r = self.tmp(expr)
+        if self.ad_order <= self._ad_depth:
+            return r
+        seeds = set()
+        for u in inputs:
+            if u.d:
+                seeds.update(u.d.keys())
+        if self._ad_cap is not None:
+            seeds = {k for k in seeds if k <= self._ad_cap}
+        if not seeds:
+            return r
+        save = (self.ad_order, self._ad_depth, self._ad_cap)
+        order = self.ad_order - self._ad_depth
+        self.ad_order = 0                     # plain arithmetic below: tangents are assembled explicitly
+        r.d = {}
+        m = len(inputs)
+        for k in sorted(seeds):
+            uk = [u.d.get(k) if u.d else None for u in inputs]
+            rk = self.lincomb([(1.0, partials[a], uk[a]) for a in range(m) if uk[a] is not None])
+            rk = V(c=rk.c, s=rk.s)
+            if order >= 2 and second is not None:
+                rk.d = {}
+                for l in sorted(x for x in seeds if x <= k):
+                    ul = [u.d.get(l) if u.d else None for u in inputs]
+                    tt = []
+                    for a in range(m):
+                        ukl = uk[a].d.get(l) if (uk[a] is not None and uk[a].d) else None
+                        if ukl is not None:
+                            tt.append((1.0, partials[a], ukl))
+                        for b in range(m):
+                            if uk[a] is not None and ul[b] is not None:
+                                tt.append((1.0, second[a][b], uk[a], ul[b]))
+                    rkl = self.lincomb(tt)
+                    if not rkl.is_zero():
+                        rk.d[l] = rkl
+                if not rk.d:
+                    rk.d = None
+            if not rk.is_zero():
+                r.d[k] = rk
+        self.ad_order, self._ad_depth, self._ad_cap = save
+        if not r.d:
+            r.d = None
+        return r
+
+    def _lincomb(self, terms: Sequence[Tuple], acc: Optional[V] = None) -> V:
+        """sum_k coef_k * x_k [* y_k ...] (+ acc).  terms: (coef, x, ...) with coef a Python float and the rest
+        V's.  Constants are folded; emits at most one statement."""
         if (acc is not None and acc.p) or any(v is not None and v.p for t in terms for v in t[1:]):
             return self._lincomb2(terms, acc)
         csum = 0.0
@@ -152,6 +247,12 @@ class Em:
                 csum += coef
             else:
                 parts.append((coef, "*".join(names)))
+        if self.ad_order and len(parts) > 1:      # product-rule expansions repeat terms: merge them
+            merged: Dict[str, float] = {}
+            for coef, name in parts:
+                key = "*".join(sorted(name.split("*")))
+                merged[key] = merged.get(key, 0.0) + coef
+            parts = [(c_, k_) for k_, c_ in merged.items() if c_ != 0.0]
         if not parts:
             return const(csum)
         if len(parts) == 1 and csum == 0.0 and parts[0][0] == 1.0 and "*" not in parts[0][1]:
@@ -265,6 +366,15 @@ class Em:
         if a.is_const:
             return const(1.0 / a.c)
         self.n_ops += 1
+        if self.ad_order > self._ad_depth and a.d:
+            r = self.tmp(f"T(1)/{a.s}")
+            save = self.ad_order
+            self.ad_order = 0
+            g1 = self.lincomb([(-1.0, r, r)])
+            g2 = self.lincomb([(-2.0, g1, r)])
+            self.ad_order = save
+            out = self.elem(r.s, [a], [g1], [[g2]])
+            return out
         return self.tmp(f"T(1)/{a.s}")
 
     def vadd(self, a: Sequence[V], b: Sequence[V]) -> List[V]:

@@ -65,7 +65,21 @@ def specs(n: int) -> List[AlgoSpec]:
                  ["q", "qd", "u"], [("d_q_qd_tau", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_qdd", lambda n: n),
         AlgoSpec("crba", "crba", "CRBA", "", algos.body_crba,
                  ["q"], [("d_q_qd", n)], [(0, 0)], "d_M", lambda n: n * n),
-    ]
+    ] + ([
+        AlgoSpec("idsva_so", "idsva_so", "IDSVA_SO", "", algos.body_idsva_so,
+                 ["q", "qd", "qdd"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_idsva_so",
+                 lambda n: 4 * n * n * n),
+        AlgoSpec("fdsva_so", "fdsva_so", "FDSVA_SO", "", algos.body_fdsva_so,
+                 ["q", "qd", "u"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_df2",
+                 lambda n: 4 * n * n * n),
+    ] if second_order_enabled(n) else [])
+
+
+def second_order_enabled(n: int) -> bool:
+    """The second-order kernels are emitted by differentiating the straight-line RNEA / CRBA at emit time; their
+    code size grows ~n^3, so they are generated for robots up to SECOND_ORDER_MAX_JOINTS joints (the reference
+    likewise switches strategy above 8-10 joints: _idsva_so.py:1, _fdsva_so.py:1)."""
+    return n <= int(os.environ.get("GRID_SECOND_ORDER_MAX_JOINTS", "8"))
 
 
 def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
@@ -210,7 +224,7 @@ def emit_launch(sp: AlgoSpec, n: int) -> str:
             f"{C}::SMEM_BYTES, num_timesteps);\n"
             f"    if (blocks <= 0) {{ cudaError_t e = cudaGetLastError(); return e != cudaSuccess ? e : cudaErrorLaunchOutOfResources; }}\n"
             f"    if (!{C}::STATE_SMEM) {{\n"
-            f"        const int cap = grid_rt::scratch_blocks();\n"
+            f"        const int cap = grid_rt::scratch_capacity(GRID_SCRATCH_BLOCKS_PER_SM);\n"
             f"        if (cap <= 0 || d_robotModel == nullptr) return cudaErrorInvalidValue;\n"
             f"        if (blocks > cap) blocks = cap;\n"
             f"    }}\n"
@@ -289,6 +303,15 @@ def host_specs(n: int) -> List[HostSpec]:
                  [("", "d_in", "h_in", "stride_q_qd")],
                  ["err = crba_launch<T>(hd_data->d_M, d_in, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
                  ("hd_data->d_M", "hd_data->h_M", "NUM_JOINTS*NUM_JOINTS")),
+        # reference names the IDSVA host function idsva_so_host (banner GRiDCodeGenerator.py:368); both names emitted
+        HostSpec("idsva_so", "", "IDSVA_SO", True, ["const int stride_q_qd_u = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd_u")],
+                 ["err = idsva_so_launch<T>(hd_data->d_idsva_so, hd_data->d_q_qd_u, stride_q_qd_u, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_idsva_so", "hd_data->h_idsva_so", "4*NUM_JOINTS*NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("fdsva_so", "", "FDSVA_SO", True, ["const int stride_q_qd_u = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd_u")],
+                 ["err = fdsva_so_launch<T>(hd_data->d_df2, hd_data->d_q_qd_u, stride_q_qd_u, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_df2", "hd_data->h_df2", "4*NUM_JOINTS*NUM_JOINTS*NUM_JOINTS")),
     ]
 
 

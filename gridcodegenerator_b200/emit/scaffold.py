@@ -72,6 +72,8 @@ struct gridData {
     T *d_M;
     T *d_dc_du;
     T *d_df_du;
+    T *d_idsva_so;   // 4 n^3 per knot, allocated only when GRID_HAS_SECOND_ORDER
+    T *d_df2;
     // CPU OUTPUTS (pinned)
     T *h_c;
     T *h_Minv;
@@ -79,6 +81,8 @@ struct gridData {
     T *h_M;
     T *h_dc_du;
     T *h_df_du;
+    T *h_idsva_so;
+    T *h_df2;
 };
 """
 
@@ -94,12 +98,9 @@ robotModel<T>* init_robotModel() {
     h_model.d_XImats = nullptr; h_model.d_topology_helpers = nullptr;
     const size_t per_block = sizeof(T) == 4 ? GRID_SCRATCH_ELEMS_PER_BLOCK_F32 : GRID_SCRATCH_ELEMS_PER_BLOCK_F64;
     if (per_block > 0) {
-        int dev = 0, sms = 0;
-        gpuErrchk(cudaGetDevice(&dev));
-        gpuErrchk(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        h_model.scratch_blocks = sms * GRID_SCRATCH_BLOCKS_PER_SM;
+        h_model.scratch_blocks = grid_rt::scratch_capacity(GRID_SCRATCH_BLOCKS_PER_SM);
+        if (h_model.scratch_blocks <= 0) gpuErrchk(cudaErrorInvalidDevice);
         gpuErrchk(cudaMalloc((void**)&h_model.d_scratch, per_block*h_model.scratch_blocks*sizeof(T)));
-        grid_rt::scratch_blocks() = h_model.scratch_blocks;
     }
     robotModel<T> *d_robotModel; gpuErrchk(cudaMalloc((void**)&d_robotModel, sizeof(robotModel<T>)));
     gpuErrchk(cudaMemcpy(d_robotModel, &h_model, sizeof(robotModel<T>), cudaMemcpyHostToDevice));
@@ -132,6 +133,13 @@ gridData<T> *init_gridData(const int num_timesteps){
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_M, n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_dc_du, 2*n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_df_du, 2*n*n*N*sizeof(T)));
+    hd_data->d_idsva_so = hd_data->d_df2 = hd_data->h_idsva_so = hd_data->h_df2 = nullptr;
+#if GRID_HAS_SECOND_ORDER
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_idsva_so, 4*n*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_df2, 4*n*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_idsva_so, 4*n*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_df2, 4*n*n*n*N*sizeof(T)));
+#endif
     return hd_data;
 }
 template <typename T, int NUM_TIMESTEPS>
@@ -163,7 +171,7 @@ void close_grid(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> 
     if (d_robotModel) {
         robotModel<T> h_model;
         gpuErrchk(cudaMemcpy(&h_model, d_robotModel, sizeof(robotModel<T>), cudaMemcpyDeviceToHost));
-        if (h_model.d_scratch) { gpuErrchk(cudaFree(h_model.d_scratch)); grid_rt::scratch_blocks() = 0; }
+        if (h_model.d_scratch) { gpuErrchk(cudaFree(h_model.d_scratch)); }
         gpuErrchk(cudaFree(d_robotModel));
     }
     if (hd_data) {
@@ -173,6 +181,8 @@ void close_grid(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> 
         gpuErrchk(cudaFreeHost(hd_data->h_q_qd_u)); gpuErrchk(cudaFreeHost(hd_data->h_q_qd)); gpuErrchk(cudaFreeHost(hd_data->h_q));
         gpuErrchk(cudaFreeHost(hd_data->h_c)); gpuErrchk(cudaFreeHost(hd_data->h_Minv)); gpuErrchk(cudaFreeHost(hd_data->h_qdd));
         gpuErrchk(cudaFreeHost(hd_data->h_M)); gpuErrchk(cudaFreeHost(hd_data->h_dc_du)); gpuErrchk(cudaFreeHost(hd_data->h_df_du));
+        if (hd_data->d_idsva_so) { gpuErrchk(cudaFree(hd_data->d_idsva_so)); gpuErrchk(cudaFree(hd_data->d_df2)); }
+        if (hd_data->h_idsva_so) { gpuErrchk(cudaFreeHost(hd_data->h_idsva_so)); gpuErrchk(cudaFreeHost(hd_data->h_df2)); }
         free(hd_data);
     }
     if (streams) {

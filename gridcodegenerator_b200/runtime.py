@@ -27,7 +27,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
               "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
-              "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9}
+              "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9, "idsva_so": 10, "fdsva_so": 11}
 
 
 def _nvcc() -> str:
@@ -53,9 +53,33 @@ def library_path(robot_name: str) -> str:
     return os.path.join(BUILD_DIR, robot_name, f"libgrid_{robot_name}.so")
 
 
-def build_library(robot, force: bool = False, verbose: bool = False) -> str:
+# translation units of one library: (GRID_PARTS bitmask, GRID_DTYPES) -- see csrc/grid_capi.cu
+CAPI_PARTS = [(0x01, 1), (0x01, 2), (0x02, 1), (0x02, 2), (0x04, 1), (0x04, 2), (0x08, 1), (0x08, 2),
+              (0x10, 1), (0x10, 2), (0x20, 1), (0x20, 2), (0x40, 1), (0x40, 2)]
+
+
+def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool) -> str:
+    obj = os.path.join(out_dir, f"capi_{part:02x}_{dtypes}.o")
+    cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f != "-shared"] + [
+        "-c", f"-I{out_dir}", f"-I{INCLUDE}", f'-DGRID_ROBOT_NAME="{name}"', f"-DGRID_PARTS={part}",
+        f"-DGRID_DTYPES={dtypes}", os.path.join(CSRC, "grid_capi.cu"), "-o", obj]
+    if verbose:
+        cmd[1:1] = ["-Xptxas", "-v"]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for robot {name} part {part:#x}/{dtypes}:\n{res.stdout[-4000:]}")
+    if verbose:
+        with open(os.path.join(out_dir, f"ptxas_{part:02x}_{dtypes}.log"), "w") as f:
+            f.write(res.stdout)
+    return obj
+
+
+def build_library(robot, force: bool = False, verbose: bool = False, pool=None) -> str:
     """Emit grid.cuh for `robot` (a robot object or the name of a shipped robot) and compile the C-ABI
-    library for sm_100a.  Returns the .so path.  Up-to-date builds are reused (digest of all sources)."""
+    library for sm_100a.  Returns the .so path.  Up-to-date builds are reused (digest of all sources).
+    The library's translation units (CAPI_PARTS) are compiled in parallel on `pool` (a
+    concurrent.futures executor shared between robots) or a private one."""
+    from concurrent.futures import ThreadPoolExecutor
     if isinstance(robot, str):
         robot = load_robot(robot)
     name = robot.name
@@ -68,17 +92,21 @@ def build_library(robot, force: bool = False, verbose: bool = False) -> str:
     stamp = os.path.join(out_dir, "digest.txt")
     if not force and os.path.exists(so) and os.path.exists(stamp) and open(stamp).read().strip() == digest:
         return so
-    cmd = [_nvcc()] + NVCC_FLAGS + [f"-I{out_dir}", f"-I{INCLUDE}", f'-DGRID_ROBOT_NAME="{name}"',
-                                    os.path.join(CSRC, "grid_capi.cu"), "-o", so]
-    if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
+    own = pool is None
+    if own:
+        pool = ThreadPoolExecutor(max_workers=min(len(CAPI_PARTS), os.cpu_count() or 1))
+    try:
+        futs = [pool.submit(_compile_part, name, out_dir, part, dt, verbose) for part, dt in CAPI_PARTS]
+        objs = [f.result() for f in futs]
+    finally:
+        if own:
+            pool.shutdown()
+    cmd = [_nvcc(), "-shared", "-Xcompiler", "-fPIC", "-gencode", "arch=compute_100a,code=sm_100a"] + objs + ["-o", so]
     res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if res.returncode != 0:
-        raise RuntimeError(f"nvcc failed for robot {name}:\n{res.stdout[-4000:]}")
-    if verbose:
-        with open(os.path.join(out_dir, "ptxas.log"), "w") as f:
-            f.write(res.stdout)
+        raise RuntimeError(f"link failed for robot {name}:\n{res.stdout[-4000:]}")
+    for o in objs:
+        os.remove(o)
     with open(stamp, "w") as f:
         f.write(digest)
     return so
@@ -117,6 +145,9 @@ class GRiDLibrary:
             getattr(L, f"grid_forward_dynamics_gradient_host_{suf}").argtypes = [vp, vp, ci, g]
             getattr(L, f"grid_aba_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_crba_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_idsva_so_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_fdsva_so_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+        self.has_second_order = bool(L.grid_has_second_order())
         L.grid_forward_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
         L.grid_inverse_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
 
@@ -241,6 +272,24 @@ class GRiDLibrary:
             self._check(getattr(self.lib, f"grid_aba_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
 
+    def _second_order(self, fn: str, x, gravity: float, out):
+        import torch
+        n = self.n
+        p, stride, B = self._dev(x, 3 * n)
+        suf = self._suf(x)
+        out = torch.empty((B, 4 * n ** 3), dtype=x.dtype, device=x.device) if out is None else out
+        with torch.cuda.device(x.device):
+            self._check(getattr(self.lib, f"grid_{fn}_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def idsva_so(self, q_qd_qdd, gravity: float = 9.81, out=None):
+        """(B, 3n) [q|qd|qdd] -> (B, 4 n^3): d2tau/dq2, d2tau/dqd2, d2tau/dqd dq, dM/dq (layout: include/grid_b200.h)."""
+        return self._second_order("idsva_so", q_qd_qdd, gravity, out)
+
+    def fdsva_so(self, q_qd_u, gravity: float = 9.81, out=None):
+        """(B, 3n) [q|qd|tau] -> (B, 4 n^3): d2qdd/dq2, d2qdd/dqd2, d2qdd/dqd dq, d2qdd/dtau dq."""
+        return self._second_order("fdsva_so", q_qd_u, gravity, out)
+
     def crba(self, q, out=None):
         import torch
         n = self.n
@@ -289,3 +338,33 @@ def get_library(robot_name: str) -> GRiDLibrary:
     if robot_name not in _LIBS:
         _LIBS[robot_name] = GRiDLibrary(robot_name)
     return _LIBS[robot_name]
+
+
+# ------------------------------------------------------------------ multi-GPU sharding
+def shard_bounds(num_knots: int, world_size: int, rank: int, align: int = 32):
+    """Contiguous slice [lo, hi) of the batch owned by `rank`.  Knot points are independent, so the batch is cut
+    into world_size contiguous slices with no exchange step; slice starts are multiples of `align` (the 32-knot
+    warp tile) so every rank's slice keeps the TMA-aligned fast path, the last rank takes the ragged tail."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad rank / world_size")
+    tiles = -(-num_knots // align)
+    per = -(-tiles // world_size)
+    lo = min(num_knots, rank * per * align)
+    hi = min(num_knots, (rank + 1) * per * align)
+    return lo, hi
+
+
+def gather_results(local, num_knots: int, group=None):
+    """Optional final gather of per-rank result slices (the only collective of the path; off the compute path).
+    local: (hi - lo, m) tensor of this rank's slice from shard_bounds().  Returns the (num_knots, m) tensor on
+    every rank.  Uses all_gather_into_tensor over equal-sized padded slices (NCCL on GPU, gloo on CPU)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    per = shard_bounds(num_knots, world, 0)[1]
+    m = local.shape[1]
+    pad = torch.zeros((per, m), dtype=local.dtype, device=local.device)
+    pad[: local.shape[0]] = local
+    out = torch.empty((world * per, m), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    return out[:num_knots]

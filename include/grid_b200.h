@@ -32,7 +32,8 @@ const char *grid_robot_name(void);
 const char *grid_last_error(void);
 int grid_abi_version(void);
 /* shared-memory bytes per CTA, threads per CTA, per-thread state elements of an algorithm's kernel
- * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv), 8 ABA, 9 CRBA;
+ * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv), 8 ABA, 9 CRBA,
+ *       10 IDSVA_SO, 11 FDSVA_SO (-1 when the library was built without second-order kernels);
  * is_f64: 0/1
  * what: 0 smem bytes, 1 threads, 2 state slots, 3 state in shared memory (0/1), 4 TMA-staged I/O (0/1),
  *       5 persistent grid size for num_knots = 1<<20 on the current device */
@@ -91,6 +92,19 @@ int grid_aba_f64(const double *d_q_qd_tau, int stride, double *d_qdd, int num_kn
  * elements of each knot's row) is read */
 int grid_crba_f32(const float *d_q, int stride, float *d_M, int num_knots, void *stream);
 int grid_crba_f64(const double *d_q, int stride, double *d_M, int num_knots, void *stream);
+
+/* ---- second-order tensors, 4 n^3 per knot, each n x n x n with index i*n*n + j*n + k
+ * grid_has_second_order(): 1 if this robot's library contains them (robots up to 8 joints by default), else the
+ * two entry points return cudaErrorNotSupported.
+ * idsva_so replaces idsva_so_host<T> (algorithms/_idsva_so.py:1030-1093; kernel :958-1028); d_q_qd_qdd: [q|qd|qdd]
+ *   [0] d2tau_i/dq_j dq_k   [1] d2tau_i/dqd_j dqd_k   [2] d2tau_i/dqd_j dq_k   [3] dM_ij/dq_k
+ * fdsva_so replaces fdsva_so<T> (algorithms/_fdsva_so.py:246-307; kernel :161-244); d_q_qd_u: [q|qd|tau]
+ *   [0] d2qdd_i/dq_j dq_k   [1] d2qdd_i/dqd_j dqd_k   [2] d2qdd_i/dqd_j dq_k   [3] d2qdd_i/dtau_j dq_k */
+int grid_has_second_order(void);
+int grid_idsva_so_f32(const float *d_q_qd_qdd, int stride, float *d_idsva_so, int num_knots, float gravity, void *stream);
+int grid_idsva_so_f64(const double *d_q_qd_qdd, int stride, double *d_idsva_so, int num_knots, double gravity, void *stream);
+int grid_fdsva_so_f32(const float *d_q_qd_u, int stride, float *d_df2, int num_knots, float gravity, void *stream);
+int grid_fdsva_so_f64(const double *d_q_qd_u, int stride, double *d_df2, int num_knots, double gravity, void *stream);
 
 /* ---- host-buffer entry points (the reference's default host semantics: H2D, kernel, D2H, blocking;
  * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / n out). */

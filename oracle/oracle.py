@@ -147,3 +147,11 @@ class Oracle:
 
     def batch_crba(self, x, nthreads=0):
         return self._batch(self.L.rbd_batch_crba, x, self.n * self.n, nthreads=nthreads)
+
+    def batch_idsva_so(self, x, gravity=9.81, nthreads=0):
+        """x: [q | qd | qdd]; out: 4 n^3 per knot (layout in rbd_oracle.c)."""
+        return self._batch(self.L.rbd_batch_idsva_so, x, 4 * self.n ** 3, ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_fdsva_so(self, x, gravity=9.81, nthreads=0):
+        """x: [q | qd | u]; out: 4 n^3 per knot (layout in rbd_oracle.c)."""
+        return self._batch(self.L.rbd_batch_fdsva_so, x, 4 * self.n ** 3, ctypes.c_double(gravity), nthreads=nthreads)

@@ -30,6 +30,28 @@ def test_emitted_bodies_match_reference_golden(name, golden, tmp_path):
         Minv = g_["Minv"][k]
         qdd_fd = Minv @ (u - g_["c0"][k])
         assert rel_err([call(lib, gen, "forward_dynamics", n, q, qd, u)], [qdd_fd]) < 1e-9
+        # ABA == FD and CRBA == inv(Minv) (no executable reference code for these two: SURVEY.md 8(c))
+        assert rel_err([call(lib, gen, "aba", n, q, qd, u)], [qdd_fd]) < 1e-8
+        M = call(lib, gen, "crba", n * n, q).reshape(n, n).T
+        assert np.abs(M @ Minv - np.eye(n)).max() < 1e-7
         # qdd+Minv input mode: feeding the FD solution reproduces grad FD
         out = call(lib, gen, "forward_dynamics_gradient_qdd_minv", 2 * n * n, q, qd, qdd_fd, cm(Minv))
         assert rel_err([out], [cm(g_["df_du"][k])]) < 1e-9
+
+
+@pytest.mark.parametrize("name", ["pendulum2", "chain3"])
+def test_second_order_bodies_match_finite_differences(name, tmp_path):
+    """IDSVA_SO / FDSVA_SO bodies (emit-time forward-mode differentiation of the straight-line RNEA / CRBA) vs the
+    oracle's central differences of the pinned first-order functions (parity unpinned upstream)."""
+    from oracle import Oracle
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    lib, gen = build_host_inners(robot, str(tmp_path))
+    orc = Oracle(robot)
+    rng = np.random.default_rng(3)
+    for _ in range(3):
+        x = rng.uniform(-1, 1, 3 * n)
+        a = call(lib, gen, "idsva_so", 4 * n ** 3, x[:n], x[n:2 * n], x[2 * n:])
+        assert rel_err([a], [orc.batch_idsva_so(x[None])[0]]) < 1e-7
+        a = call(lib, gen, "fdsva_so", 4 * n ** 3, x[:n], x[n:2 * n], x[2 * n:])
+        assert rel_err([a], [orc.batch_fdsva_so(x[None])[0]]) < 1e-7

@@ -100,6 +100,79 @@ def test_fd_grad_vs_oracle_fp32(name, B, torch_cuda):
                    orc.batch_rnea_grad(x64, use_qdd=True)) < TOL32
 
 
+@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("hyq", 16384), ("atlas", 200), ("branched6", 97), ("slider3", 64)])
+def test_aba_crba_fp32(name, B, torch_cuda):
+    """ABA and CRBA (reference algorithms/_aba.py, _crba.py; BASELINE configs 3 and 4).  The reference has no
+    executable CPU code for them ("parity unpinned"): the oracle's textbook versions are checked
+    against the pinned functions in tests/test_oracle_golden.py, and here additionally ABA == FD kernel and
+    CRBA * Minv == I with the library's own (pinned) Minv."""
+    torch = torch_cuda
+    lib, orc = _lib(name), _oracle(name)
+    n = lib.n
+    rng = np.random.default_rng(7)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    X = torch.from_numpy(x32).cuda()
+    f = lambda t: t.cpu().numpy().astype(np.float64)
+    sub = np.unique(np.concatenate([np.arange(min(B, 256)), rng.choice(B, min(B, 256), replace=False)]))
+    x64 = x32[sub].astype(np.float64)
+    qdd = lib.aba(X)
+    assert rel_err(f(qdd)[sub], orc.batch_aba(x64)) < TOL32
+    assert rel_err(f(qdd), f(lib.forward_dynamics(X))) < TOL32
+    M = lib.crba(X[:, :n].contiguous())
+    assert rel_err(f(M)[sub], orc.batch_crba(x64)) < TOL32
+    assert torch.equal(lib.crba(X), M)                                          # strided q_qd_u buffer
+    Minv = lib.direct_minv(X[:, :n].contiguous()).view(B, n, n).double()
+    eye = torch.eye(n, dtype=torch.float64, device="cuda")
+    assert float((M.view(B, n, n).double() @ Minv - eye).abs().max()) < 2e-3
+
+
+@pytest.mark.parametrize("name,B", [("iiwa14", 300), ("branched6", 70)])
+def test_second_order_fp32_fp64(name, B, torch_cuda):
+    """IDSVA_SO / FDSVA_SO (reference algorithms/_idsva_so.py, _fdsva_so.py; BASELINE config 5).  Parity is
+    UNPINNED by the reference (no executable CPU code upstream); the oracle is fp64 central differences of the
+    pinned first-order functions (oracle/rbd_oracle.c: rbd_idsva_so, rbd_fdsva_so), good to ~1e-8, so:
+    fp64 kernel vs oracle 1e-6, fp32 kernel vs fp64 kernel 1e-4."""
+    torch = torch_cuda
+    lib, orc = _lib(name), _oracle(name)
+    assert lib.has_second_order
+    n = lib.n
+    x = np.random.default_rng(11).uniform(-1, 1, (B, 3 * n)).astype(np.float32).astype(np.float64)
+    X64 = torch.from_numpy(x).cuda()
+    X32 = X64.float()
+    sub = np.arange(0, B, 7)
+    for fn, ofn in (("idsva_so", orc.batch_idsva_so), ("fdsva_so", orc.batch_fdsva_so)):
+        o64 = getattr(lib, fn)(X64).cpu().numpy()
+        o32 = getattr(lib, fn)(X32).cpu().numpy().astype(np.float64)
+        assert o64.shape == (B, 4 * n ** 3)
+        assert rel_err(o64[sub], ofn(x[sub])) < 1e-6, fn
+        assert rel_err(o32, o64) < TOL32, fn
+    # symmetry of the pure second derivatives
+    T = lib.fdsva_so(X64).view(B, 4, n, n, n)
+    assert float((T[:, 0] - T[:, 0].transpose(2, 3)).abs().max()) == 0.0
+    assert float((T[:, 1] - T[:, 1].transpose(2, 3)).abs().max()) == 0.0
+    # d2qdd/dtau dq is the derivative of Minv: contracting with tau-independent checks is covered by the oracle
+
+
+def test_second_order_absent_for_large_robots(torch_cuda):
+    torch = torch_cuda
+    lib = _lib("hyq")
+    assert not lib.has_second_order
+    x = torch.zeros((4, 3 * lib.n), dtype=torch.float32, device="cuda")
+    with pytest.raises(RuntimeError, match="second-order"):
+        lib.idsva_so(x)
+
+
+@pytest.mark.parametrize("name,B", [("iiwa14", 130), ("hyq", 64), ("atlas", 33)])
+def test_aba_crba_fp64(name, B, torch_cuda):
+    torch = torch_cuda
+    lib, orc = _lib(name), _oracle(name)
+    n = lib.n
+    x = np.random.default_rng(8).uniform(-1, 1, (B, 3 * n))
+    X = torch.from_numpy(x).cuda()
+    assert rel_err(lib.aba(X).cpu().numpy(), orc.batch_aba(x)) < TOL64 * 10
+    assert rel_err(lib.crba(X[:, :n].contiguous()).cpu().numpy(), orc.batch_crba(x)) < TOL64
+
+
 @pytest.mark.parametrize("name,B", [("iiwa14", 257), ("hyq", 96), ("atlas", 40)])
 def test_fd_grad_vs_oracle_fp64(name, B, torch_cuda):
     torch = torch_cuda

@@ -19,5 +19,6 @@ $SHORT > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu1.log 2>&1
 $SHORT > $OUT/${TAG}_plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:forward_dynamics_gradient -s 5 -c 2 -f -o $OUT/${TAG}_prof $SHORT > $OUT/${TAG}_ncu2.log 2>&1
+ncu --set full --clock-control none --cache-control none --import-source on -k regex:forward_dynamics_gradient -s 5 -c 2 -f -o $OUT/${TAG}_prof_warm $SHORT > $OUT/${TAG}_ncu3.log 2>&1
 tail -2 $OUT/${TAG}_ncu2.log
 ls -la $OUT | tail -20
