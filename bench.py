@@ -35,6 +35,27 @@ L2_BYTES = 126 * 1024 * 1024
 METRIC = "grad-FD knot-points/sec (iiwa14, batch 65536 per GPU)"
 
 
+def _measured_traffic():
+    """DRAM bytes per launch of the headline kernel from the committed ncu --set full capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "dram_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p))
+        except Exception:
+            return None
+    return None
+
+
+def _emitted_ops():
+    """mul+add operations per knot in the emitted grad-FD body (the kernel's executed FP32 work, after constant
+    folding; packed pair operations count twice)."""
+    try:
+        from gridcodegenerator_b200 import GRiDCodeGenerator, load_robot
+        return int(GRiDCodeGenerator(load_robot(ROBOT))._body("forward_dynamics_gradient").n_ops)
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -247,6 +268,8 @@ def run_ours(args):
         model_tflops = MODEL_FLOPS_PER_KNOT * BATCH / (kernel_ms * 1e-3) / 1e12
         cpu_v, cores, done, cpu_dt = cpu_reference_leg(args.cpu_seconds)
         info = lib.kernel_info("forward_dynamics_gradient")
+        traffic = _measured_traffic()
+        ops = _emitted_ops()
         line = {
             "metric": METRIC, "value": value, "unit": "knots/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
@@ -256,11 +279,16 @@ def run_ours(args):
                        "l2": f"rotating {nsets} input/output buffer sets ({nsets * set_bytes >> 20} MB > 126 MB L2)",
                        "kernel": info, "persistent_blocks": lib.persistent_blocks("forward_dynamics_gradient")},
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": which,
+                         "frac": achieved_gbs / hbm_peak,
+                         "traffic": traffic["bytes_per_launch"] if traffic else None,
+                         "traffic_source": traffic.get("source") if traffic else None, "peak_source": which,
                          "kernel": "forward_dynamics_gradient_kernel<float>", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_knot": BYTES_PER_KNOT,
                          "fp32": {"model_flops_per_knot": MODEL_FLOPS_PER_KNOT, "achieved_tflops": model_tflops,
                                   "peak_tflops": fp32_peak, "frac": model_tflops / fp32_peak,
+                                  "executed_flops_per_knot": ops,
+                                  "executed_tflops": (ops * BATCH / (kernel_ms * 1e-3) / 1e12) if ops else None,
+                                  "executed_frac": (ops * BATCH / (kernel_ms * 1e-3) / 1e12 / fp32_peak) if ops else None,
                                   "note": "path is FP32-pipe-bound (SURVEY 8(d)); model FLOPs = dense 6x6 count of "
                                           "the reference algorithm, peak = 148 SM x 128 lanes x 2 x max SM clock"}},
             "cpu_baseline": {"value": cpu_v, "unit": "knots/s", "cores": cores, "kind": "port",

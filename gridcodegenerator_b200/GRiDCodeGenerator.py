@@ -35,7 +35,7 @@ class GRiDCodeGenerator:
             raise NotImplementedError("floating-base robots are out of scope of the B200 hot path (SURVEY.md 2.1 row 18)")
         self.model = Model(robotObj)
         self._bodies: Dict[str, _algos.Body] = {}
-        self._specs = {sp.fn + sp.tag: sp for sp in _hdr.specs(self.model.n)}
+        self._specs = {sp.fn + sp.tag: sp for sp in _hdr.specs(self.model.n, robotObj.get_total_leaf_nodes())}
 
     # ------------------------------------------------- emission core (L1 API)
     # reference helpers/_code_generation_helpers.py:1-40 (same names, same behaviour)
@@ -157,7 +157,8 @@ def _bind(key: str):
 
 
 for _key in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-             "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so"):
+             "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so", "end_effector_pose",
+             "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
     _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner_temp_mem_size", _t)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner", _i)
@@ -179,7 +180,8 @@ GRiDCodeGenerator.gen_crba_device_temp_mem_size = GRiDCodeGenerator.gen_crba_inn
 # ----------------------------------------------------------------- file scaffolding
 from .emit import scaffold as _sc  # noqa: E402
 
-ALGO_ORDER = ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+ALGO_ORDER = ("end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian",
+              "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
               "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so")
 
 

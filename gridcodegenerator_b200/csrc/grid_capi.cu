@@ -22,6 +22,7 @@
 #define PART_ABA_CRBA 0x10
 #define PART_IDSVA 0x20
 #define PART_FDSVA 0x40
+#define PART_EE 0x80
 #ifndef GRID_PARTS
 #define GRID_PARTS 0xFF
 #endif
@@ -182,7 +183,7 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
 // ---- per-part kernel introspection, dispatched from grid_kernel_info (defined in the core f32 part)
 #define DECL_INFO(NAME) HIDDEN long grid_capi_info_##NAME##_f32(int algo, int what); \
                         HIDDEN long grid_capi_info_##NAME##_f64(int algo, int what);
-DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(aba_crba) DECL_INFO(idsva) DECL_INFO(fdsva)
+DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(aba_crba) DECL_INFO(idsva) DECL_INFO(fdsva) DECL_INFO(ee)
 
 // Everything below is instantiated for the dtypes of this translation unit through GRID_FOR_DTYPES(X):
 #if (GRID_DTYPES & 1) && (GRID_DTYPES & 2)
@@ -242,9 +243,10 @@ GRID_FOR_DTYPES(X_CORE)
 #if (GRID_DTYPES & 1)
 extern "C" {
 int grid_num_joints(void) { return N; }
+int grid_num_ees(void) { return grid::NUM_EES; }
 const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
 const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
-int grid_abi_version(void) { return 3; }
+int grid_abi_version(void) { return 4; }
 int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
 long grid_kernel_info(int algo, int is_f64, int what) {
 #define DISPATCH(NAME) return is_f64 ? grid_capi_info_##NAME##_f64(algo, what) : grid_capi_info_##NAME##_f32(algo, what);
@@ -256,6 +258,7 @@ long grid_kernel_info(int algo, int is_f64, int what) {
         case 8: case 9: DISPATCH(aba_crba)
         case 10: DISPATCH(idsva)
         case 11: DISPATCH(fdsva)
+        case 12: case 13: case 14: DISPATCH(ee)
     }
     return -1;
 }
@@ -451,4 +454,48 @@ X_SO(fdsva_so, fdsva_so_launch, fdsva_so_cfg, fdsva_so_algo, fdsva_so_kernel, 11
 #define X_FDSVA(SUF, T) X_SO_STUB(fdsva, SUF, T)
 #endif
 GRID_FOR_DTYPES(X_FDSVA)
+#endif
+
+// =============================================================== end-effector pose, gradient, Hessian
+#if HAS(PART_EE)
+namespace {
+template <typename T>
+int ee_pose_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_end_effector_pose", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)));
+    return fail(grid::end_effector_pose_launch<T>(d_out, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+int ee_grad_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_end_effector_pose_gradient", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)));
+    return fail(grid::end_effector_pose_gradient_launch<T>(d_out, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+int ee_hess_impl(const T* d_q, int stride, T* d_grad, T* d_hess, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_end_effector_pose_gradient_hessian", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_hess)));
+    if (d_grad) {
+        cudaError_t e = grid::end_effector_pose_gradient_launch<T>(d_grad, d_q, stride, m, nk, st);
+        if (e != cudaSuccess) return fail(e, fn);
+    }
+    return fail(grid::end_effector_pose_gradient_hessian_launch<T>(d_hess, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+long info_ee(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    typedef void (*K)(T*, const T*, const int, RM, const int);
+    switch (algo) {
+        case 12: GRID_INFO(end_effector_pose_cfg, end_effector_pose_algo, static_cast<K>(end_effector_pose_kernel<T>))
+        case 13: GRID_INFO(end_effector_pose_gradient_cfg, end_effector_pose_gradient_algo, static_cast<K>(end_effector_pose_gradient_kernel<T>))
+        case 14: GRID_INFO(end_effector_pose_gradient_hessian_cfg, end_effector_pose_gradient_hessian_algo, static_cast<K>(end_effector_pose_gradient_hessian_kernel<T>))
+    }
+    return -1;
+}
+}  // namespace
+#define X_EE(SUF, T)                                                                                               \
+    long grid_capi_info_ee_##SUF(int algo, int what) { return info_ee<T>(algo, what); }                            \
+    extern "C" int grid_end_effector_pose_##SUF(const T* a, int st, T* o, int nk, void* s) { return ee_pose_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_end_effector_pose_gradient_##SUF(const T* a, int st, T* o, int nk, void* s) { return ee_grad_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_end_effector_pose_gradient_hessian_##SUF(const T* a, int st, T* g, T* h, int nk, void* s) { \
+        return ee_hess_impl<T>(a, st, g, h, nk, s); }
+GRID_FOR_DTYPES(X_EE)
 #endif

@@ -60,6 +60,7 @@ class Ctx:
         em = self.em
         self.q = self.read_vec(q_ptr, "q_")
         self.X = []
+        self.trig = []
         for j, jd in enumerate(self.m.joints):
             if jd.revolute:
                 em.line(f"T sn{j}, cs{j}; grid_sincos(q_{j}, &sn{j}, &cs{j});")
@@ -74,6 +75,7 @@ class Ctx:
                     self.q[j] = V(s=self.q[j].s, d={j: ONE})
                 tr = Trig(None, None, self.q[j])
             self.X.append(Xform(jd, tr))
+            self.trig.append((tr.s, tr.c, tr.q))
 
     def seed_vec(self, vec: Sequence[V], first_seed: int) -> List[V]:
         """Mark vec[j] as AD seed first_seed + j."""
@@ -873,3 +875,91 @@ def body_fdsva_so(model: Model) -> Body:
                 _out(em, 2 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in range(n)]))
                 _out(em, 3 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner_t[L]) for L in range(n)]))
     return Body("fdsva_so_inner", "", cx, "second-order forward dynamics tensors (4 n^3)")
+
+
+# ================================================================= EE pose
+def ee_poses(cx: Ctx, order: int):
+    """Pose [x y z roll pitch yaw] of every leaf link frame in the base frame (reference
+    algorithms/_eepose_gradient_hessian.py:31-160): product of the homogeneous joint transforms down each chain,
+    then roll = atan2(R21, R22), pitch = -atan2(R20, sqrt(R21^2 + R22^2)), yaw = atan2(R10, R00) (:150-157).
+    With order 1 / 2 the pose entries carry their gradient / Hessian with respect to q (seed k = joint k); the
+    reference derives those by hand from dXhom / d2Xhom (:511-538, :985-1058), here they are the emit-time
+    tangents of the same chain product."""
+    from .spatial import hom_tables
+    em, m, n = cx.em, cx.m, cx.n
+    save = em.ad_order
+    em.ad_order = order
+    H = hom_tables(m.robot)
+    Tc: Dict[int, List[List[V]]] = {}
+    for j in range(n):
+        H0, Hs, Hc, Hq = H[j]
+        sn, cs, qv = cx.trig[j]
+
+        def ent(r, c):
+            e = []
+            if H0[r, c] != 0.0:
+                e.append((float(H0[r, c]), None))
+            if Hs[r, c] != 0.0:
+                e.append((float(Hs[r, c]), sn))
+            if Hc[r, c] != 0.0:
+                e.append((float(Hc[r, c]), cs))
+            if Hq[r, c] != 0.0:
+                e.append((float(Hq[r, c]), qv))
+            return e
+        p = m.parent[j]
+        T = [[None] * 4 for _ in range(3)]
+        for r in range(3):
+            for c in range(4):
+                if p < 0:
+                    T[r][c] = em.lincomb([(coef, f) if f is not None else (coef, ONE) for coef, f in ent(r, c)])
+                else:
+                    terms = []
+                    for k in range(3):
+                        for coef, f in ent(k, c):
+                            terms.append((coef, f, Tc[p][r][k]))
+                    T[r][c] = em.lincomb(terms, Tc[p][r][3] if c == 3 else None)
+        Tc[j] = T
+    poses = []
+    for e_ in m.robot.get_leaf_nodes():
+        T = Tc[e_]
+        roll = em.atan2(T[2][1], T[2][2])
+        sq = em.sqrt(em.lincomb([(1.0, T[2][1], T[2][1]), (1.0, T[2][2], T[2][2])]))
+        pitch = em.neg(em.atan2(T[2][0], sq))
+        yaw = em.atan2(T[1][0], T[0][0])
+        poses.append([T[0][3], T[1][3], T[2][3], roll, pitch, yaw])
+    em.ad_order = save
+    return poses
+
+
+def body_end_effector_pose(model: Model) -> Body:
+    """out[6*ee + o], o in x y z roll pitch yaw (reference :142-159)."""
+    cx = _second_order_ctx(model)
+    for e_, pose in enumerate(ee_poses(cx, 0)):
+        for o, v in enumerate(pose):
+            _out(cx.em, 6 * e_ + o, v)
+    return Body("end_effector_pose_inner", "", cx, "end-effector poses")
+
+
+def body_end_effector_pose_gradient(model: Model) -> Body:
+    """out[(ee*n + j)*6 + o] = d pose_o / d q_j (reference s_deePos[6*deeInd + outputInd], :517-535)."""
+    cx = _second_order_ctx(model)
+    n = model.n
+    for e_, pose in enumerate(ee_poses(cx, 1)):
+        for j in range(n):
+            for o, v in enumerate(pose):
+                _out(cx.em, (e_ * n + j) * 6 + o, _d1(v, j))
+    return Body("end_effector_pose_gradient_inner", "", cx, "gradient of the end-effector poses")
+
+
+def body_end_effector_pose_gradient_hessian(model: Model) -> Body:
+    """Hessian[(ee*6 + o)*n*n + i*n + j] = d2 pose_o / dq_i dq_j (reference s_d2eePos[outputInd*n*n + i*n + j],
+    :1024, :1056).  The gradient half of the reference kernel's two outputs (:1108) comes from the gradient kernel:
+    the host tier / C ABI launch both."""
+    cx = _second_order_ctx(model)
+    n = model.n
+    for e_, pose in enumerate(ee_poses(cx, 2)):
+        for o, v in enumerate(pose):
+            for i in range(n):
+                for j in range(n):
+                    _out(cx.em, (e_ * 6 + o) * n * n + i * n + j, _d2(v, i, j))
+    return Body("end_effector_pose_gradient_hessian_inner", "", cx, "Hessian of the end-effector poses")

@@ -377,6 +377,45 @@ class Em:
             return out
         return self.tmp(f"T(1)/{a.s}")
 
+    def _plain(self, fn):
+        """Run fn() with differentiation switched off (for the explicit partials handed to elem)."""
+        save = self.ad_order
+        self.ad_order = 0
+        try:
+            return fn()
+        finally:
+            self.ad_order = save
+
+    def sqrt(self, a: V) -> V:
+        if a.is_const:
+            return const(a.c ** 0.5)
+        r = self.tmp(f"sqrt({a.s})")
+        if not (self.ad_order > self._ad_depth and a.d):
+            return r
+        g1 = self._plain(lambda: self.lincomb([(0.5, self.recip(r))]))              # 1 / (2 sqrt a)
+        g2 = self._plain(lambda: self.lincomb([(-0.5, g1, self.recip(a))]))         # -1 / (4 a sqrt a)
+        return self.elem(r.s, [a], [g1], [[g2]])
+
+    def atan2(self, y: V, x: V) -> V:
+        if y.is_const and x.is_const:
+            import math
+            return const(math.atan2(y.c, x.c))
+        from_v = lambda v: lit(v.c) if v.is_const else v.s
+        r = self.tmp(f"atan2({from_v(y)}, {from_v(x)})")
+        if not (self.ad_order > self._ad_depth and (y.d or x.d)):
+            return r
+
+        def partials():
+            w = self.recip(self.lincomb([(1.0, x, x), (1.0, y, y)]))
+            gy = self.lincomb([(1.0, x, w)])
+            gx = self.lincomb([(-1.0, y, w)])
+            gyy = self.lincomb([(-2.0, gy, y, w)])          # -2 x y w^2
+            gxx = self.lincomb([(-2.0, gx, x, w)])          #  2 x y w^2
+            gxy = self.lincomb([(1.0, y, y, w, w), (-1.0, x, x, w, w)])
+            return gy, gx, gyy, gxx, gxy
+        gy, gx, gyy, gxx, gxy = self._plain(partials)
+        return self.elem(r.s, [y, x], [gy, gx], [[gyy, gxy], [gxy, gxx]])
+
     def vadd(self, a: Sequence[V], b: Sequence[V]) -> List[V]:
         return [self.add(x, y) for x, y in zip(a, b)]
 

@@ -37,8 +37,17 @@ class AlgoSpec:
     extra_kernel_params: str = ""
 
 
-def specs(n: int) -> List[AlgoSpec]:
+def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
+    ee = num_ees
     return [
+        AlgoSpec("end_effector_pose", "end_effector_pose", "EE", "", algos.body_end_effector_pose,
+                 ["q"], [("d_q", n)], [(0, 0)], "d_eePos", lambda n: 6 * ee, uses_gravity=False),
+        AlgoSpec("end_effector_pose_gradient", "end_effector_pose_gradient", "DEE", "",
+                 algos.body_end_effector_pose_gradient,
+                 ["q"], [("d_q", n)], [(0, 0)], "d_deePos", lambda n: 6 * ee * n, uses_gravity=False),
+        AlgoSpec("end_effector_pose_gradient_hessian", "end_effector_pose_gradient_hessian", "D2EE", "",
+                 algos.body_end_effector_pose_gradient_hessian,
+                 ["q"], [("d_q", n)], [(0, 0)], "d_d2eePos", lambda n: 6 * ee * n * n, uses_gravity=False),
         AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "", lambda m: algos.body_inverse_dynamics(m, False),
                  ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_c", lambda n: n),
         AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "_qdd", lambda m: algos.body_inverse_dynamics(m, True),
@@ -258,9 +267,13 @@ class HostSpec:
     h2d: List[Tuple[str, str, str, str]]   # (condition or "", d_ptr, h_ptr, elements per knot)
     launch: List[str]               # lines performing the launch into `err`
     d2h: Tuple[str, str, str]       # (d_ptr, h_ptr, elements per knot)
+    extra_d2h: List[Tuple[str, str, str]] = field(default_factory=list)
 
 
 def host_specs(n: int) -> List[HostSpec]:
+    qsel = ["const int stride_q = USE_COMPRESSED_MEM ? NUM_JOINTS : 3*NUM_JOINTS;",
+            "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q : hd_data->d_q_qd_u;",
+            "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q : hd_data->h_q_qd_u;"]
     comp = ["const int stride_q_qd = USE_COMPRESSED_MEM ? 2*NUM_JOINTS : 3*NUM_JOINTS;",
             "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q_qd : hd_data->d_q_qd_u;",
             "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q_qd : hd_data->h_q_qd_u;"]
@@ -303,6 +316,20 @@ def host_specs(n: int) -> List[HostSpec]:
                  [("", "d_in", "h_in", "stride_q_qd")],
                  ["err = crba_launch<T>(hd_data->d_M, d_in, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
                  ("hd_data->d_M", "hd_data->h_M", "NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("end_effector_pose", ", bool USE_COMPRESSED_MEM = false", "EE_POS", False, qsel,
+                 [("", "d_in", "h_in", "stride_q")],
+                 ["err = end_effector_pose_launch<T>(hd_data->d_eePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                 ("hd_data->d_eePos", "hd_data->h_eePos", "6*NUM_EES")),
+        HostSpec("end_effector_pose_gradient", ", bool USE_COMPRESSED_MEM = false", "DEE_POS", False, qsel,
+                 [("", "d_in", "h_in", "stride_q")],
+                 ["err = end_effector_pose_gradient_launch<T>(hd_data->d_deePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                 ("hd_data->d_deePos", "hd_data->h_deePos", "6*NUM_EES*NUM_JOINTS")),
+        HostSpec("end_effector_pose_gradient_hessian", ", bool USE_COMPRESSED_MEM = false", "D2EE_POS", False, qsel,
+                 [("", "d_in", "h_in", "stride_q")],
+                 ["err = end_effector_pose_gradient_launch<T>(hd_data->d_deePos, d_in, stride_q, d_robotModel, num_timesteps, 0);",
+                  "if (err == cudaSuccess) err = end_effector_pose_gradient_hessian_launch<T>(hd_data->d_d2eePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                 ("hd_data->d_d2eePos", "hd_data->h_d2eePos", "6*NUM_EES*NUM_JOINTS*NUM_JOINTS"),
+                 extra_d2h=[("hd_data->d_deePos", "hd_data->h_deePos", "6*NUM_EES*NUM_JOINTS")]),
         # reference names the IDSVA host function idsva_so_host (banner GRiDCodeGenerator.py:368); both names emitted
         HostSpec("idsva_so", "", "IDSVA_SO", True, ["const int stride_q_qd_u = 3*NUM_JOINTS;"],
                  [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd_u")],
@@ -341,8 +368,8 @@ def emit_host(hs: HostSpec, mode: int) -> str:
         out.append("    clock_gettime(CLOCK_MONOTONIC, &end);")
         out.append(f'    printf("Single Call {hs.label} %fus\\n", time_delta_us_timespec(start, end)/static_cast<double>(num_timesteps));')
     if mode != 2:
-        d, h, cnt = hs.d2h
-        out.append(f"    gpuErrchk(cudaMemcpy({h}, {d}, size_t({cnt})*num_timesteps*sizeof(T), cudaMemcpyDeviceToHost));")
+        for d, h, cnt in [hs.d2h] + list(hs.extra_d2h):
+            out.append(f"    gpuErrchk(cudaMemcpy({h}, {d}, size_t({cnt})*num_timesteps*sizeof(T), cudaMemcpyDeviceToHost));")
         out.append("    gpuErrchk(cudaDeviceSynchronize());")
     out.append("}")
     return "\n".join(out) + "\n\n"

@@ -72,6 +72,9 @@ struct gridData {
     T *d_M;
     T *d_dc_du;
     T *d_df_du;
+    T *d_eePos;
+    T *d_deePos;
+    T *d_d2eePos;
     T *d_idsva_so;   // 4 n^3 per knot, allocated only when GRID_HAS_SECOND_ORDER
     T *d_df2;
     // CPU OUTPUTS (pinned)
@@ -81,6 +84,9 @@ struct gridData {
     T *h_M;
     T *h_dc_du;
     T *h_df_du;
+    T *h_eePos;
+    T *h_deePos;
+    T *h_d2eePos;
     T *h_idsva_so;
     T *h_df2;
 };
@@ -133,6 +139,12 @@ gridData<T> *init_gridData(const int num_timesteps){
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_M, n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_dc_du, 2*n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_df_du, 2*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_eePos, 6*NUM_EES*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_deePos, 6*NUM_EES*n*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_d2eePos, 6*NUM_EES*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_eePos, 6*NUM_EES*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_deePos, 6*NUM_EES*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_d2eePos, 6*NUM_EES*n*n*N*sizeof(T)));
     hd_data->d_idsva_so = hd_data->d_df2 = hd_data->h_idsva_so = hd_data->h_df2 = nullptr;
 #if GRID_HAS_SECOND_ORDER
     gpuErrchk(cudaMalloc((void**)&hd_data->d_idsva_so, 4*n*n*n*N*sizeof(T)));
@@ -181,6 +193,8 @@ void close_grid(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> 
         gpuErrchk(cudaFreeHost(hd_data->h_q_qd_u)); gpuErrchk(cudaFreeHost(hd_data->h_q_qd)); gpuErrchk(cudaFreeHost(hd_data->h_q));
         gpuErrchk(cudaFreeHost(hd_data->h_c)); gpuErrchk(cudaFreeHost(hd_data->h_Minv)); gpuErrchk(cudaFreeHost(hd_data->h_qdd));
         gpuErrchk(cudaFreeHost(hd_data->h_M)); gpuErrchk(cudaFreeHost(hd_data->h_dc_du)); gpuErrchk(cudaFreeHost(hd_data->h_df_du));
+        gpuErrchk(cudaFree(hd_data->d_eePos)); gpuErrchk(cudaFree(hd_data->d_deePos)); gpuErrchk(cudaFree(hd_data->d_d2eePos));
+        gpuErrchk(cudaFreeHost(hd_data->h_eePos)); gpuErrchk(cudaFreeHost(hd_data->h_deePos)); gpuErrchk(cudaFreeHost(hd_data->h_d2eePos));
         if (hd_data->d_idsva_so) { gpuErrchk(cudaFree(hd_data->d_idsva_so)); gpuErrchk(cudaFree(hd_data->d_df2)); }
         if (hd_data->h_idsva_so) { gpuErrchk(cudaFreeHost(hd_data->h_idsva_so)); gpuErrchk(cudaFreeHost(hd_data->h_df2)); }
         free(hd_data);

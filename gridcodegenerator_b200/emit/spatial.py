@@ -211,3 +211,27 @@ def inertia_mul(em: Em, I, v: Sequence[V], acc: Optional[Sequence[V]] = None) ->
 
 def unit(S: int, val: V) -> List[V]:
     return [val if k == S else ZERO for k in range(6)]
+
+
+def hom_tables(robot):
+    """Per joint the homogeneous child->parent transform as Xhom_j(q) = H0 + sin(q) Hs + cos(q) Hc + q Hq
+    (4x4 numeric), recovered by sampling the robot's sympy matrices (reference consumer:
+    helpers/_topology_helpers.py:333-504, robot.get_Xmats_hom_ordered_by_id)."""
+    mats = robot.get_Xmats_hom_ordered_by_id()
+    out = []
+    for j, M in enumerate(mats):
+        syms = list(M.free_symbols)
+        ev = lambda val: np.array(M.subs({s_: val for s_ in syms}).evalf(), dtype=np.float64).reshape(4, 4)
+        revolute = int(np.argmax(np.abs(robot.get_S_by_id(j)))) < 3
+        Z = np.zeros((4, 4))
+        if revolute:
+            A, B, C = ev(0.0), ev(np.pi / 2), ev(np.pi)
+            H0, Hc = _snap((A + C) / 2), _snap((A - C) / 2)
+            Hs = _snap(B - H0)
+            out.append((H0, Hs, Hc, Z))
+            th = 0.37
+            assert np.abs(H0 + np.sin(th) * Hs + np.cos(th) * Hc - ev(th)).max() < 1e-9
+        else:
+            A, B = ev(0.0), ev(1.0)
+            out.append((_snap(A), Z, Z, _snap(B - A)))
+    return out

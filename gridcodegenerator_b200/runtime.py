@@ -18,7 +18,7 @@ from .robot import load_robot
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-BUILD_DIR = os.path.join(_PKG, "_build")
+BUILD_DIR = os.environ.get("GRID_BUILD_DIR") or os.path.join(_PKG, "_build")   # override: A/B variant builds
 CSRC = os.path.join(_PKG, "csrc")
 INCLUDE = os.path.join(_ROOT, "include")
 
@@ -27,7 +27,8 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
               "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
-              "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9, "idsva_so": 10, "fdsva_so": 11}
+              "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9, "idsva_so": 10, "fdsva_so": 11, "end_effector_pose": 12,
+              "end_effector_pose_gradient": 13, "end_effector_pose_gradient_hessian": 14}
 
 
 def _nvcc() -> str:
@@ -55,7 +56,7 @@ def library_path(robot_name: str) -> str:
 
 # translation units of one library: (GRID_PARTS bitmask, GRID_DTYPES) -- see csrc/grid_capi.cu
 CAPI_PARTS = [(0x01, 1), (0x01, 2), (0x02, 1), (0x02, 2), (0x04, 1), (0x04, 2), (0x08, 1), (0x08, 2),
-              (0x10, 1), (0x10, 2), (0x20, 1), (0x20, 2), (0x40, 1), (0x40, 2)]
+              (0x10, 1), (0x10, 2), (0x20, 1), (0x20, 2), (0x40, 1), (0x40, 2), (0x80, 3)]
 
 
 def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool) -> str:
@@ -147,7 +148,11 @@ class GRiDLibrary:
             getattr(L, f"grid_crba_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_idsva_so_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_fdsva_so_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_end_effector_pose_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_end_effector_pose_gradient_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_end_effector_pose_gradient_hessian_{suf}").argtypes = [vp, ci, vp, vp, ci, vp]
         self.has_second_order = bool(L.grid_has_second_order())
+        self.num_ees = int(L.grid_num_ees())
         L.grid_forward_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
         L.grid_inverse_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
 
@@ -289,6 +294,36 @@ class GRiDLibrary:
     def fdsva_so(self, q_qd_u, gravity: float = 9.81, out=None):
         """(B, 3n) [q|qd|tau] -> (B, 4 n^3): d2qdd/dq2, d2qdd/dqd2, d2qdd/dqd dq, d2qdd/dtau dq."""
         return self._second_order("fdsva_so", q_qd_u, gravity, out)
+
+    def end_effector_pose(self, q, out=None):
+        """(B, >=n) rows starting with q -> (B, 6*num_ees) [x y z roll pitch yaw] per end effector."""
+        import torch
+        p, stride, B = self._dev(q, self.n)
+        out = torch.empty((B, 6 * self.num_ees), dtype=q.dtype, device=q.device) if out is None else out
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_end_effector_pose_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
+        return out
+
+    def end_effector_pose_gradient(self, q, out=None):
+        """-> (B, 6*num_ees*n), index (ee*n + j)*6 + o."""
+        import torch
+        p, stride, B = self._dev(q, self.n)
+        out = torch.empty((B, 6 * self.num_ees * self.n), dtype=q.dtype, device=q.device) if out is None else out
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_end_effector_pose_gradient_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
+        return out
+
+    def end_effector_pose_gradient_hessian(self, q):
+        """-> (gradient (B, 6*num_ees*n), Hessian (B, 6*num_ees*n*n) with index (ee*6 + o)*n*n + i*n + j)."""
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q, n)
+        g = torch.empty((B, 6 * self.num_ees * n), dtype=q.dtype, device=q.device)
+        h = torch.empty((B, 6 * self.num_ees * n * n), dtype=q.dtype, device=q.device)
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_end_effector_pose_gradient_hessian_{self._suf(q)}")(
+                p, stride, g.data_ptr(), h.data_ptr(), B, self._stream()))
+        return g, h
 
     def crba(self, q, out=None):
         import torch

@@ -28,12 +28,14 @@ extern "C" {
 
 /* ---- introspection (reference constants NUM_JOINTS etc., GRiDCodeGenerator.py:86-111) ---- */
 int grid_num_joints(void);
+int grid_num_ees(void);           /* number of leaf links = end effectors (reference NUM_EES, GRiDCodeGenerator.py:96) */
 const char *grid_robot_name(void);
 const char *grid_last_error(void);
 int grid_abi_version(void);
 /* shared-memory bytes per CTA, threads per CTA, per-thread state elements of an algorithm's kernel
  * algo: 0 ID, 1 ID(qdd), 2 MINV, 3 FD, 4 ID_DU, 5 ID_DU(qdd), 6 FD_DU, 7 FD_DU(qdd,Minv), 8 ABA, 9 CRBA,
- *       10 IDSVA_SO, 11 FDSVA_SO (-1 when the library was built without second-order kernels);
+ *       10 IDSVA_SO, 11 FDSVA_SO (-1 when the library was built without second-order kernels),
+ *       12 EE pose, 13 EE pose gradient, 14 EE pose Hessian;
  * is_f64: 0/1
  * what: 0 smem bytes, 1 threads, 2 state slots, 3 state in shared memory (0/1), 4 TMA-staged I/O (0/1),
  *       5 persistent grid size for num_knots = 1<<20 on the current device */
@@ -105,6 +107,23 @@ int grid_idsva_so_f32(const float *d_q_qd_qdd, int stride, float *d_idsva_so, in
 int grid_idsva_so_f64(const double *d_q_qd_qdd, int stride, double *d_idsva_so, int num_knots, double gravity, void *stream);
 int grid_fdsva_so_f32(const float *d_q_qd_u, int stride, float *d_df2, int num_knots, float gravity, void *stream);
 int grid_fdsva_so_f64(const double *d_q_qd_u, int stride, double *d_df2, int num_knots, double gravity, void *stream);
+
+/* ---- end-effector (leaf link frame) poses [x y z roll pitch yaw] in the base frame, their gradient and Hessian
+ * with respect to q; only q (first n elements of each knot's row) is read.
+ * replace end_effector_pose<T,..>, end_effector_pose_gradient<T,..>, end_effector_pose_gradient_hessian<T,..>
+ * (algorithms/_eepose_gradient_hessian.py:253-310, :632-690, :1157-1220; kernels :197-251, :576-630, :1097-1155)
+ *   d_eePos  [6*ee + o]                      6 NUM_EES per knot
+ *   d_deePos [(ee*n + j)*6 + o]              d pose_o / dq_j          (reference s_deePos[6*deeInd + outputInd])
+ *   d_d2eePos[(ee*6 + o)*n*n + i*n + j]      d2 pose_o / dq_i dq_j    (reference s_d2eePos[outputInd*n*n + i*n + j])
+ * gradient_hessian fills both outputs like the reference kernel (d_deePos may be NULL to skip the gradient). */
+int grid_end_effector_pose_f32(const float *d_q, int stride, float *d_eePos, int num_knots, void *stream);
+int grid_end_effector_pose_f64(const double *d_q, int stride, double *d_eePos, int num_knots, void *stream);
+int grid_end_effector_pose_gradient_f32(const float *d_q, int stride, float *d_deePos, int num_knots, void *stream);
+int grid_end_effector_pose_gradient_f64(const double *d_q, int stride, double *d_deePos, int num_knots, void *stream);
+int grid_end_effector_pose_gradient_hessian_f32(const float *d_q, int stride, float *d_deePos, float *d_d2eePos,
+                                                int num_knots, void *stream);
+int grid_end_effector_pose_gradient_hessian_f64(const double *d_q, int stride, double *d_deePos, double *d_d2eePos,
+                                                int num_knots, void *stream);
 
 /* ---- host-buffer entry points (the reference's default host semantics: H2D, kernel, D2H, blocking;
  * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / n out). */

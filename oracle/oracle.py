@@ -61,6 +61,14 @@ class Oracle:
         if not self._h:
             raise RuntimeError("rbd_model_create failed (n too large?)")
         self.L = L
+        # homogeneous transforms + leaves for the end-effector functions
+        from gridcodegenerator_b200.emit.spatial import hom_tables
+        H = hom_tables(robot)
+        hs = [np.ascontiguousarray(np.stack([h[i] for h in H]), dtype=np.float64) for i in range(4)]
+        leaves = np.ascontiguousarray(robot.get_leaf_nodes(), dtype=np.int32)
+        self.nleaf = len(leaves)
+        L.rbd_model_set_hom.argtypes = [ctypes.c_void_p, _dp, _dp, _dp, _dp, ctypes.c_int, _ip]
+        L.rbd_model_set_hom(self._h, *[_d(a) for a in hs], ctypes.c_int(self.nleaf), leaves.ctypes.data_as(_ip))
 
     def __del__(self):
         try:
@@ -155,3 +163,15 @@ class Oracle:
     def batch_fdsva_so(self, x, gravity=9.81, nthreads=0):
         """x: [q | qd | u]; out: 4 n^3 per knot (layout in rbd_oracle.c)."""
         return self._batch(self.L.rbd_batch_fdsva_so, x, 4 * self.n ** 3, ctypes.c_double(gravity), nthreads=nthreads)
+
+    def batch_ee_pose(self, x, nthreads=0):
+        """x: rows starting with q; out[6*ee + o]."""
+        return self._batch(self.L.rbd_batch_ee_pose, x, 6 * self.nleaf, nthreads=nthreads)
+
+    def batch_ee_pose_gradient(self, x, nthreads=0):
+        """out[(ee*n + j)*6 + o] (central differences of the pose)."""
+        return self._batch(self.L.rbd_batch_ee_pose_gradient, x, 6 * self.nleaf * self.n, nthreads=nthreads)
+
+    def batch_ee_pose_hessian(self, x, nthreads=0):
+        """out[(ee*6 + o)*n*n + i*n + j] (second central differences of the pose, ~1e-7 accurate)."""
+        return self._batch(self.L.rbd_batch_ee_pose_hessian, x, 6 * self.nleaf * self.n ** 2, nthreads=nthreads)

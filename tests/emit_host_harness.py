@@ -35,12 +35,14 @@ static inline double_pair pneg(double_pair a) { return mkp<double>(-a.x, -a.y); 
 """
 
 
-def build_host_inners(robot, workdir=None):
+def build_host_inners(robot, workdir=None, second_order=False):
     g = GRiDCodeGenerator(robot)
     n = g.model.n
     src = [PRELUDE]
     wrappers = []
     for name, sp in g._specs.items():
+        if name in ("idsva_so", "fdsva_so") and not second_order:
+            continue          # ~n^3 code: compiled for the host only by the test that checks them
         body = g._body(name)
         src.append(hdr.emit_inner(sp, body))
         ins = ", ".join(f"const double* {p}" for p in sp.inner_inputs)

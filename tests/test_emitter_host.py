@@ -46,7 +46,7 @@ def test_second_order_bodies_match_finite_differences(name, tmp_path):
     from oracle import Oracle
     robot = load_robot(name)
     n = robot.get_num_pos()
-    lib, gen = build_host_inners(robot, str(tmp_path))
+    lib, gen = build_host_inners(robot, str(tmp_path), second_order=True)
     orc = Oracle(robot)
     rng = np.random.default_rng(3)
     for _ in range(3):
@@ -55,3 +55,23 @@ def test_second_order_bodies_match_finite_differences(name, tmp_path):
         assert rel_err([a], [orc.batch_idsva_so(x[None])[0]]) < 1e-7
         a = call(lib, gen, "fdsva_so", 4 * n ** 3, x[:n], x[n:2 * n], x[2 * n:])
         assert rel_err([a], [orc.batch_fdsva_so(x[None])[0]]) < 1e-7
+
+
+@pytest.mark.parametrize("name", ["chain3", "branched6", "iiwa14"])
+def test_end_effector_bodies(name, tmp_path):
+    """EE pose / gradient / Hessian bodies vs the oracle's chain product + RPY restatement and its central
+    differences (reference algorithms/_eepose_gradient_hessian.py:142-159, :511-538, :985-1058)."""
+    from oracle import Oracle
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    lib, gen = build_host_inners(robot, str(tmp_path))
+    orc = Oracle(robot)
+    ne = orc.nleaf
+    rng = np.random.default_rng(4)
+    for _ in range(3):
+        q = rng.uniform(-1, 1, n)
+        assert rel_err([call(lib, gen, "end_effector_pose", 6 * ne, q)], [orc.batch_ee_pose(q[None])[0]]) < TOL
+        assert rel_err([call(lib, gen, "end_effector_pose_gradient", 6 * ne * n, q)],
+                       [orc.batch_ee_pose_gradient(q[None])[0]]) < 1e-8
+        assert rel_err([call(lib, gen, "end_effector_pose_gradient_hessian", 6 * ne * n * n, q)],
+                       [orc.batch_ee_pose_hessian(q[None])[0]]) < 1e-5

@@ -153,6 +153,37 @@ def test_second_order_fp32_fp64(name, B, torch_cuda):
     # d2qdd/dtau dq is the derivative of Minv: contracting with tau-independent checks is covered by the oracle
 
 
+@pytest.mark.parametrize("name,B", [("iiwa14", 1000), ("hyq", 200), ("atlas", 64), ("branched6", 50)])
+def test_end_effector_pose_gradient_hessian(name, B, torch_cuda):
+    """EE pose / gradient / Hessian (reference algorithms/_eepose_gradient_hessian.py; BASELINE config 5) against
+    the oracle's restatement of the chain product + RPY formulas and its central differences (parity unpinned
+    upstream).  fp64 kernel vs oracle: pose 1e-10, gradient 1e-7, Hessian 1e-5 (finite-difference accuracy);
+    fp32 kernel vs fp64 kernel 1e-4 for the pose / gradient, Hessian on knots away from the RPY singularity."""
+    torch = torch_cuda
+    lib, orc = _lib(name), _oracle(name)
+    n, ne = lib.n, lib.num_ees
+    x = np.random.default_rng(12).uniform(-1, 1, (B, n)).astype(np.float32).astype(np.float64)
+    X64 = torch.from_numpy(x).cuda()
+    X32 = X64.float()
+    sub = np.arange(0, B, 5)
+    p64 = lib.end_effector_pose(X64)
+    g64, h64 = lib.end_effector_pose_gradient_hessian(X64)
+    assert p64.shape == (B, 6 * ne) and g64.shape == (B, 6 * ne * n) and h64.shape == (B, 6 * ne * n * n)
+    assert rel_err(p64.cpu().numpy()[sub], orc.batch_ee_pose(x[sub])) < TOL64
+    assert rel_err(g64.cpu().numpy()[sub], orc.batch_ee_pose_gradient(x[sub])) < 1e-7
+    assert rel_err(h64.cpu().numpy()[sub], orc.batch_ee_pose_hessian(x[sub])) < 1e-5
+    assert torch.equal(lib.end_effector_pose_gradient(X64), g64)
+    H = h64.view(B, ne * 6, n, n)
+    assert float((H - H.transpose(2, 3)).abs().max()) == 0.0
+    p32 = lib.end_effector_pose(X32)
+    g32, h32 = lib.end_effector_pose_gradient_hessian(X32)
+    assert rel_err(p32.cpu().numpy(), p64.cpu().numpy()) < TOL32
+    # RPY derivatives grow like 1/cos(pitch)^k: compare relative to the Hessian's own scale per knot
+    assert rel_err(g32.cpu().numpy(), g64.cpu().numpy()) < 1e-3
+    hs = h64.abs().amax(dim=1).clamp(min=1.0)
+    assert float(((h32.double() - h64).abs().amax(dim=1) / hs).median()) < TOL32
+
+
 def test_second_order_absent_for_large_robots(torch_cuda):
     torch = torch_cuda
     lib = _lib("hyq")
