@@ -224,6 +224,7 @@ def gen_add_constants_helpers(self):
              "const int SUGGESTED_THREADS = 32; // single-warp CTAs: warps never synchronise with each other"]
     per4, per8 = _scratch_constants(self)
     lines += [f"#define GRID_HAS_SECOND_ORDER {int(_hdr.second_order_enabled(n))}",
+              f"#define GRID_HAS_EE_HESSIAN {int(_hdr.ee_hessian_enabled(n))}",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F64 = {per8};",
               "const int GRID_SCRATCH_BLOCKS_PER_SM = 2;"]

@@ -107,12 +107,12 @@ template <class A>
 __host__ __device__ constexpr int in_n(int s) { return s == 0 ? A::IN0 : (s == 1 ? A::IN1 : A::IN2); }
 
 // Shared-memory footprint (bytes) of one CTA of NT threads.
-template <class A, typename T, int NT, bool STATE_SMEM, bool STAGED>
+template <class A, typename T, int NT, bool STATE_SMEM, int STAGED>
 constexpr size_t tile_smem_bytes() {
     size_t state = STATE_SMEM ? align16(size_t(A::SLOTS) * NT * sizeof(T)) : 0;
     size_t per_warp = 0;
     if (STAGED) {
-        for (int s = 0; s < MAX_STREAMS; s++) per_warp += 2 * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+        for (int s = 0; s < MAX_STREAMS; s++) per_warp += STAGED * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
         per_warp += align16(size_t(TILE) * A::OUT * sizeof(T));
         per_warp += 16;  // two mbarriers
     }
@@ -131,10 +131,13 @@ __device__ __forceinline__ void cta_sync() {
 #define GRID_SYNC() grid_rt::cta_sync<NT>()
 
 // A CTA of NT threads (NT/32 warps) walks the batch in rounds; in each round warp w of CTA b owns tile
-// round*gridDim.x*(NT/32) + b*(NT/32) + w (32 knot points, one per lane).  All warps of the CTA execute every
+// (round*(NT/32) + w)*gridDim.x + b (32 knot points, one per lane).  All warps of the CTA execute every
 // round, with dummy work when their tile does not exist, because the body contains CTA-wide lockstep barriers.
 // The kernel must be launched with exactly NT threads per block.
-template <class A, typename T, int NT, bool STATE_SMEM, bool STAGED>
+// STAGED: 0 = plain loads / stores; 2 = TMA-staged with double-buffered inputs (next tile's load overlaps this
+// tile's math); 1 = TMA-staged with one input buffer (next load issued after the body; frees shared memory for
+// more lockstep warps when the batch fits one or two rounds anyway).
+template <class A, typename T, int NT, bool STATE_SMEM, int STAGED>
 __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* smem) {
     constexpr int NWARPS = NT / 32;
     if (blockDim.x != NT) return;                  // launch contract: exactly NT threads per CTA
@@ -143,7 +146,9 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     const int num_tiles = (a.num_knots + TILE - 1) / TILE;
     const int tiles_per_round = gridDim.x * NWARPS;
     const int rounds = (num_tiles + tiles_per_round - 1) / tiles_per_round;
-    const int first = blockIdx.x * NWARPS + warp;
+    // warp w of CTA b owns tiles (r*NWARPS + w)*gridDim.x + b: the tiles of the last, partial round spread evenly
+    // over the SMs (every SM keeps ~the same number of busy warps) instead of leaving whole SMs idle
+    const int first = warp * gridDim.x + blockIdx.x;
 
     T* S;
     size_t off = 0;
@@ -172,7 +177,10 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
 #pragma unroll
     for (int s = 0; s < MAX_STREAMS; s++)
 #pragma unroll
-        for (int b = 0; b < 2; b++) { in_off[s][b] = per_warp; per_warp += align16(size_t(TILE) * in_n<A>(s) * sizeof(T)); }
+        for (int b = 0; b < 2; b++) {
+            in_off[s][b] = (b < STAGED) ? per_warp : in_off[s][0];
+            if (b < STAGED) per_warp += align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+        }
     const size_t out_off = per_warp;
     per_warp += align16(size_t(TILE) * A::OUT * sizeof(T));
     const size_t bar_off = per_warp;
@@ -212,12 +220,12 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     bool store_pending = false;
     if (tile_is_tma(first) && lane == 0) issue_load(first, 0);
 
-    for (int r = 0; r < rounds; r++, buf ^= 1) {
+    for (int r = 0; r < rounds; r++, buf = (STAGED == 2) ? (buf ^ 1) : 0) {
         const int tile = first + r * tiles_per_round;
         const int next = tile + tiles_per_round;
         const bool valid = tile < num_tiles;
         const bool tma = tile_is_tma(tile);
-        if (tile_is_tma(next) && lane == 0) issue_load(next, buf ^ 1);
+        if (STAGED == 2 && tile_is_tma(next) && lane == 0) issue_load(next, buf ^ 1);
         const int nvalid = valid ? min(TILE, a.num_knots - tile * TILE) : 0;
         const T* x[MAX_STREAMS];
 #pragma unroll
@@ -244,6 +252,11 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
         }
         A::template run<NT>(out_s + lane * A::OUT, x[0], x[1], x[2], S, a.gravity);
         __syncwarp();
+        if (STAGED == 1 && tile_is_tma(next)) {      // single input buffer: every lane is done reading it
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) issue_load(next, 0);
+        }
         if (tma) {
             fence_proxy_async();
             __syncwarp();
@@ -291,8 +304,8 @@ static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
     }
     if (plan->blocks_per_sm <= 0) return 0;
     const int tiles = (num_knots + TILE - 1) / TILE;
-    const int warps_per_block = threads / 32;
-    const int want = (tiles + warps_per_block - 1) / warps_per_block;
+    const int want = tiles;      // small batches: one tile per SM first (tile -> CTA mapping is round-robin over CTAs)
+    (void)threads;
     const int cap = plan->blocks_per_sm * plan->sms;
     return want < cap ? want : cap;
 }

@@ -248,6 +248,7 @@ const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
 const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
 int grid_abi_version(void) { return 4; }
 int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
+int grid_has_ee_hessian(void) { return GRID_HAS_EE_HESSIAN; }
 long grid_kernel_info(int algo, int is_f64, int what) {
 #define DISPATCH(NAME) return is_f64 ? grid_capi_info_##NAME##_f64(algo, what) : grid_capi_info_##NAME##_f32(algo, what);
     switch (algo) {
@@ -471,12 +472,17 @@ int ee_grad_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
 }
 template <typename T>
 int ee_hess_impl(const T* d_q, int stride, T* d_grad, T* d_hess, int nk, void* s) {
+#if GRID_HAS_EE_HESSIAN
     GRID_CHECK_ARGS("grid_end_effector_pose_gradient_hessian", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_hess)));
     if (d_grad) {
         cudaError_t e = grid::end_effector_pose_gradient_launch<T>(d_grad, d_q, stride, m, nk, st);
         if (e != cudaSuccess) return fail(e, fn);
     }
     return fail(grid::end_effector_pose_gradient_hessian_launch<T>(d_hess, d_q, stride, m, nk, st), fn);
+#else
+    grid_capi_last_error() = "grid_end_effector_pose_gradient_hessian: this library was built without the EE Hessian kernel";
+    return static_cast<int>(cudaErrorNotSupported);
+#endif
 }
 template <typename T>
 long info_ee(int algo, int what) {
@@ -486,7 +492,9 @@ long info_ee(int algo, int what) {
     switch (algo) {
         case 12: GRID_INFO(end_effector_pose_cfg, end_effector_pose_algo, static_cast<K>(end_effector_pose_kernel<T>))
         case 13: GRID_INFO(end_effector_pose_gradient_cfg, end_effector_pose_gradient_algo, static_cast<K>(end_effector_pose_gradient_kernel<T>))
+#if GRID_HAS_EE_HESSIAN
         case 14: GRID_INFO(end_effector_pose_gradient_hessian_cfg, end_effector_pose_gradient_hessian_algo, static_cast<K>(end_effector_pose_gradient_hessian_kernel<T>))
+#endif
     }
     return -1;
 }

@@ -572,6 +572,58 @@ def body_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> Body:
     return Body("inverse_dynamics_gradient_inner", "", cx, "[dc/dq | dc/dqd], column-major n x 2n")
 
 
+def ltdl_factor(cx: Ctx, Mv: Dict[tuple, V]):
+    """Sparse L^T D L factorisation of the joint-space inertia matrix (Featherstone RBDA table 6.3): M = L^T D L with
+    L unit lower triangular and L[k][i] != 0 only for i an ancestor of k, so branch sparsity is kept.  Returns
+    (L: dict (k, i) -> V, Dinv: list of V).  Used by grad FD to apply M^-1 without forming it: the reference
+    computes Minv explicitly (algorithms/_direct_minv.py) and multiplies (_forward_dynamics_gradient.py:48-62);
+    factor + solves give the same result in ~half the operations of the analytical Minv."""
+    em, m, n = cx.em, cx.m, cx.n
+    H: Dict[tuple, V] = {}
+    for i in range(n):
+        H[(i, i)] = Mv[(i, i)]
+        for j in m.ancestors[i]:
+            H[(i, j)] = Mv[(min(i, j), max(i, j))]          # lower triangle, row i, column j = ancestor
+    L: Dict[tuple, V] = {}
+    Dinv: List[V] = [ZERO] * n
+    for k in range(n - 1, -1, -1):
+        Dinv[k] = em.recip(H[(k, k)])
+        i = m.parent[k]
+        while i >= 0:
+            a = em.mul(H[(k, i)], Dinv[k])
+            j = i
+            while j >= 0:
+                H[(i, j)] = em.lincomb([(1.0, H[(i, j)]), (-1.0, a, H[(k, j)])])
+                j = m.parent[j]
+            L[(k, i)] = a
+            i = m.parent[i]
+    return L, Dinv
+
+
+def ltdl_solve(cx: Ctx, L, Dinv, b: Sequence[V], sign: float = 1.0) -> List[V]:
+    """x = sign * M^-1 b with M = L^T D L (b scalar- or pair-valued)."""
+    em, m, n = cx.em, cx.m, cx.n
+    x = list(b)
+    for i in range(n - 1, -1, -1):                      # x = L^-T b
+        j = m.parent[i]
+        while j >= 0:
+            x[j] = em.lincomb([(1.0, x[j]), (-1.0, L[(i, j)], x[i])])
+            j = m.parent[j]
+    x = [em.lincomb([(sign, x[i], Dinv[i])]) for i in range(n)]
+    for i in range(n):                                  # x = L^-1 x
+        j = m.parent[i]
+        terms = [(1.0, x[i])]
+        while j >= 0:
+            terms.append((-1.0, L[(i, j)], x[j]))
+            j = m.parent[j]
+        x[i] = em.lincomb(terms)
+    return x
+
+
+def fdgrad_solver_policy() -> str:
+    return os.environ.get("GRID_FDGRAD_SOLVER", "ltdl")
+
+
 def body_forward_dynamics_gradient(model: Model) -> Body:
     cx = Ctx(model)
     em, n = cx.em, model.n
@@ -581,20 +633,45 @@ def body_forward_dynamics_gradient(model: Model) -> Body:
     em.comment("---- pass 1: bias forces c = RNEA(q, qd, 0)")
     rnea_forward(cx, qd, None, keep=False)
     c = rnea_backward(cx, qd, keep_f=False)
-    em.comment("---- Minv")
-    articulated_inertias(cx)
-    Minv = minv_columns(cx)
-    qdd = fd_finish(cx, Minv, u, c)
-    store_minv(cx, Minv)
-    keys = list(Minv.keys())
+    if fdgrad_solver_policy() == "minv":
+        em.comment("---- Minv")
+        articulated_inertias(cx)
+        Minv = minv_columns(cx)
+        qdd = fd_finish(cx, Minv, u, c)
+        store_minv(cx, Minv)
+        keys = list(Minv.keys())
+    else:
+        em.comment("---- M = CRBA(q), M = L^T D L")
+        Mv = crba_matrix(cx)
+        L, Dinv = ltdl_factor(cx, Mv)
+        for k_, v_ in L.items():
+            em.store(("L",) + k_, v_)
+        for i_, v_ in enumerate(Dinv):
+            em.store(("Dinv2", i_, 0), v_)
+        qdd = ltdl_solve(cx, L, Dinv, [em.sub(u[j], c[j]) for j in range(n)])
     em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
     rnea_forward(cx, qd, qdd, keep=True)
     rnea_backward(cx, qd, keep_f=True)
     em.comment("---- grad RNEA columns and df_du = -Minv dc_du")
 
     def sink(c_, dc):
-        Mi = load_minv(cx, keys)
-        _sink_product(em, n, c_, dc, lambda r, k: minv_get(Mi, r, k))
+        if fdgrad_solver_policy() == "minv":
+            Mi = load_minv(cx, keys)
+            _sink_product(em, n, c_, dc, lambda r, k: minv_get(Mi, r, k))
+            return
+        Ll = {k_: em.load(("L",) + k_) for k_ in L}
+        Dl = [em.load(("Dinv2", i_, 0)) for i_ in range(n)]
+        if all(not isinstance(e, tuple) for e in dc):
+            x = ltdl_solve(cx, Ll, Dl, dc, sign=-1.0)
+            for r in range(n):
+                a, b = _halves(em, x[r])
+                _out(em, c_ * n + r, a)
+                _out(em, (n + c_) * n + r, b)
+        else:
+            for h in (0, 1):
+                x = ltdl_solve(cx, Ll, Dl, [_halves(em, e)[h] for e in dc], sign=-1.0)
+                for r in range(n):
+                    _out(em, (h * n + c_) * n + r, x[r])
 
     rnea_grad_columns(cx, qd, sink)
     return Body("forward_dynamics_gradient_inner", "", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]")

@@ -45,9 +45,11 @@ def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
         AlgoSpec("end_effector_pose_gradient", "end_effector_pose_gradient", "DEE", "",
                  algos.body_end_effector_pose_gradient,
                  ["q"], [("d_q", n)], [(0, 0)], "d_deePos", lambda n: 6 * ee * n, uses_gravity=False),
+    ] + ([
         AlgoSpec("end_effector_pose_gradient_hessian", "end_effector_pose_gradient_hessian", "D2EE", "",
                  algos.body_end_effector_pose_gradient_hessian,
                  ["q"], [("d_q", n)], [(0, 0)], "d_d2eePos", lambda n: 6 * ee * n * n, uses_gravity=False),
+    ] if ee_hessian_enabled(n) else []) + [
         AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "", lambda m: algos.body_inverse_dynamics(m, False),
                  ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_c", lambda n: n),
         AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "_qdd", lambda m: algos.body_inverse_dynamics(m, True),
@@ -84,6 +86,12 @@ def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
     ] if second_order_enabled(n) else [])
 
 
+def ee_hessian_enabled(n: int) -> bool:
+    """The EE Hessian has 6 EE n^2 outputs per knot (27 000 for Atlas); it is generated for robots up to
+    GRID_EE_HESSIAN_MAX_JOINTS joints (default 16: iiwa14, HyQ), the pose and its gradient for every robot."""
+    return n <= int(os.environ.get("GRID_EE_HESSIAN_MAX_JOINTS", "16"))
+
+
 def second_order_enabled(n: int) -> bool:
     """The second-order kernels are emitted by differentiating the straight-line RNEA / CRBA at emit time; their
     code size grows ~n^3, so they are generated for robots up to SECOND_ORDER_MAX_JOINTS joints (the reference
@@ -92,23 +100,27 @@ def second_order_enabled(n: int) -> bool:
 
 
 def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
-    """(NT, STATE_SMEM, STAGED) for one algorithm and scalar size.
+    """(NT, STATE_SMEM, STAGED) for one algorithm and scalar size.  STAGED: 0 = plain loads/stores, 2 = TMA-staged
+    I/O with double-buffered inputs, 1 = TMA-staged with a single input buffer (chosen when that admits more warps).
 
     One CTA per SM with as many warps as shared memory (per-thread state + per-warp TMA staging) and the
-    register file (255 registers/thread -> 8 warps) allow.  The warps of the CTA run in lockstep through the
-    straight-line body (GRID_SYNC points), which is what keeps the kernel off the instruction-fetch limit."""
+    register file allow.  The warps of the CTA run in lockstep through the straight-line body (GRID_SYNC points),
+    which is what keeps the kernel off the instruction-fetch limit."""
     a16 = lambda x: (x + 15) & ~15
     state_w = a16(slots * 32 * sizeof)
-    stage_w = sum(2 * a16(32 * e * sizeof) for e in in_elems) + a16(32 * out_elems * sizeof) + 16
-    fit = (SMEM_LIMIT - 16) // (state_w + stage_w)
-    if os.environ.get("GRID_FORCE_UNSTAGED") == "1":
-        fit = 0
-    if fit >= 1:
-        return 32 * min(MAX_WARPS, fit), True, True
+    best = None
+    if os.environ.get("GRID_FORCE_UNSTAGED") != "1":
+        for nbuf in (2, 1):
+            stage_w = sum(nbuf * a16(32 * e * sizeof) for e in in_elems) + a16(32 * out_elems * sizeof) + 16
+            fit = (SMEM_LIMIT - 16) // (state_w + stage_w)
+            if fit >= 1 and (best is None or min(MAX_WARPS, fit) > best[0]):
+                best = (min(MAX_WARPS, fit), nbuf)
+    if best is not None:
+        return 32 * best[0], True, best[1]
     fit = (SMEM_LIMIT - 16) // state_w
     if fit >= 1:
-        return 32 * min(MAX_WARPS, fit), True, False
-    return 32 * MAX_WARPS_SCRATCH, False, False
+        return 32 * min(MAX_WARPS, fit), True, 0
+    return 32 * MAX_WARPS_SCRATCH, False, 0
 
 
 def algo_struct_name(sp: AlgoSpec) -> str:
@@ -153,7 +165,7 @@ def emit_config(sp: AlgoSpec, body: algos.Body, n: int) -> str:
     return (f"template <typename T>\nstruct {name} {{\n"
             f"    static constexpr int NT = sizeof(T) == 4 ? {c4[0]} : {c8[0]};\n"
             f"    static constexpr bool STATE_SMEM = sizeof(T) == 4 ? {b(c4[1])} : {b(c8[1])};\n"
-            f"    static constexpr bool STAGED = sizeof(T) == 4 ? {b(c4[2])} : {b(c8[2])};\n"
+            f"    static constexpr int STAGED = sizeof(T) == 4 ? {int(c4[2])} : {int(c8[2])};\n"
             f"    static constexpr size_t SMEM_BYTES = grid_rt::tile_smem_bytes<{A}<T>, T, NT, STATE_SMEM, STAGED>();\n"
             f"}};\n\n")
 
@@ -194,7 +206,11 @@ def emit_device_and_kernel(sp: AlgoSpec, n: int) -> str:
         dev = (f"template <typename T>\n__device__ __forceinline__\n"
                f"void {sp.fn}{sp.tag}_device(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) {{\n"
                f"    {tl}(a, s_mem);\n}}\n\n")
-    ker = (f"template <typename T>\n__global__ void __launch_bounds__({C}::NT, 1)\n"
+    # register budget: __launch_bounds__(NT, 1) lets ptxas round the per-thread limit down coarsely (128 for 448
+    # threads); __maxnreg__ pins it to the largest multiple of 8 that still fits one CTA in the 64 K register file
+    bounds = (f"__maxnreg__(({C}::NT * 255 <= 65536) ? 255 : (65536 / {C}::NT / 8 * 8))"
+              if os.environ.get("GRID_USE_MAXNREG", "1") == "1" else f"__launch_bounds__({C}::NT, 1)")
+    ker = (f"template <typename T>\n__global__ void {bounds}\n"
            f"{sp.fn}_kernel({kernel_params(sp)}) {{\n"
            f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"
            f"    grid_rt::TileArgs<T> a;\n" + "\n".join(fill) + "\n"

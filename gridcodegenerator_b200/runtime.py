@@ -152,6 +152,7 @@ class GRiDLibrary:
             getattr(L, f"grid_end_effector_pose_gradient_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_end_effector_pose_gradient_hessian_{suf}").argtypes = [vp, ci, vp, vp, ci, vp]
         self.has_second_order = bool(L.grid_has_second_order())
+        self.has_ee_hessian = bool(L.grid_has_ee_hessian())
         self.num_ees = int(L.grid_num_ees())
         L.grid_forward_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]
         L.grid_inverse_dynamics_host_f32.argtypes = [vp, vp, ci, ctypes.c_float]

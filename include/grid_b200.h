@@ -116,6 +116,7 @@ int grid_fdsva_so_f64(const double *d_q_qd_u, int stride, double *d_df2, int num
  *   d_deePos [(ee*n + j)*6 + o]              d pose_o / dq_j          (reference s_deePos[6*deeInd + outputInd])
  *   d_d2eePos[(ee*6 + o)*n*n + i*n + j]      d2 pose_o / dq_i dq_j    (reference s_d2eePos[outputInd*n*n + i*n + j])
  * gradient_hessian fills both outputs like the reference kernel (d_deePos may be NULL to skip the gradient). */
+int grid_has_ee_hessian(void);   /* 0: robot above 16 joints, gradient_hessian returns cudaErrorNotSupported */
 int grid_end_effector_pose_f32(const float *d_q, int stride, float *d_eePos, int num_knots, void *stream);
 int grid_end_effector_pose_f64(const double *d_q, int stride, double *d_eePos, int num_knots, void *stream);
 int grid_end_effector_pose_gradient_f32(const float *d_q, int stride, float *d_deePos, int num_knots, void *stream);
