@@ -336,8 +336,11 @@ def fd_finish(cx: Ctx, Minv, u: Sequence[V], c: Sequence[V]) -> List[V]:
 
 # ============================================================== grad RNEA
 def pairs_policy() -> bool:
-    """Carry the dq and dqd derivative columns of a joint as one packed pair (FFMA2 on sm_100a)."""
-    return os.environ.get("GRID_EMIT_PAIRS", "1") != "0"
+    """Carry the dq and dqd derivative columns of a joint as one packed pair (FFMA2 on sm_100a).
+    Off by default: measured on B200 (profiles/r01c_ab.log) FFMA2 occupies the FMA pipe for two cycles, so packing
+    saves issue slots and code bytes (8160 -> 6808 SASS instructions for iiwa14 grad FD) but not pipe time, and the
+    pair (un)packing MOVs make it 6 % slower than the scalar form (32.7 vs 30.7 us at 65536 knots)."""
+    return os.environ.get("GRID_EMIT_PAIRS", "0") != "0"
 
 
 def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):

@@ -9,7 +9,8 @@ from gridcodegenerator_b200.runtime import GRiDLibrary
 lib = GRiDLibrary("iiwa14", build=False)
 n, B = lib.n, 65536
 x = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (B, 3 * n)).astype(np.float32)).cuda()
-only = sys.argv[1:] 
+only = [a for a in sys.argv[1:] if not a.startswith("--")]
+if "--time" in sys.argv: only = ["none"]
 def run(name, fn):
     if only and name not in only: return
     for _ in range(4): fn()
@@ -26,3 +27,36 @@ run("aba", lambda: lib.aba(x))
 run("crba", lambda: lib.crba(q))
 if hasattr(lib, "has_ee_hessian"):
     run("ee", lambda: lib.end_effector_pose_gradient_hessian(q))
+
+# ---- timing mode (python tools/kernel_times.py --time): CUDA-graph replay of 20 launches per kernel, CUDA events
+if "--time" in sys.argv:
+    import json
+    outs = {}
+    def timed(name, fn):
+        fn(); torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            fn()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g, stream=s):
+                for _ in range(20): fn()
+        for _ in range(3): g.replay()
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) / 20)
+        print(json.dumps({"kernel": name, "us": best * 1e3}), flush=True)
+    o_c = torch.empty((B, n), dtype=torch.float32, device="cuda")
+    o_m = torch.empty((B, n * n), dtype=torch.float32, device="cuda")
+    o_g = torch.empty((B, 2 * n * n), dtype=torch.float32, device="cuda")
+    timed("id", lambda: lib.inverse_dynamics(q_qd, qdd, out=o_c))
+    timed("minv", lambda: lib.direct_minv(q, out=o_m))
+    timed("fd", lambda: lib.forward_dynamics(x, out=o_c))
+    timed("id_du", lambda: lib.inverse_dynamics_gradient(q_qd, qdd, out=o_g))
+    timed("fd_du", lambda: lib.forward_dynamics_gradient(x, out=o_g))
+    timed("fd_du_qm", lambda: lib.forward_dynamics_gradient_qdd_minv(q_qd, qdd, Minv, out=o_g))
+    timed("aba", lambda: lib.aba(x, out=o_c))
+    timed("crba", lambda: lib.crba(q, out=o_m))
