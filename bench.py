@@ -188,6 +188,7 @@ def run_ours(args):
     import torch.distributed as dist
 
     rank, world, local = _dist()
+    os.dup2(2, 1)     # stray library output (NCCL banner) goes to stderr; the JSON line is written by _emit()
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -301,7 +302,7 @@ def run_ours(args):
             "gpu_launches": args.steps,
             "clocks": clocks,
         }
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -319,6 +320,14 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
+
+
+def _emit(line: dict):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = os.dup(1)
 
 
 if __name__ == "__main__":

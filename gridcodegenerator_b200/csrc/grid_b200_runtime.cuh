@@ -22,8 +22,19 @@
 
 namespace grid_rt {
 
+// Accurate sincos (the reference emits double-precision sin/cos then casts, helpers/_topology_helpers.py:194-195; the
+// fast __sincosf would not hold 1e-4 through a depth-7 chain).  By default ONE out-of-line copy per kernel:
+// inlined, every joint carries its own range-reduction slow path (~100 SASS instructions each), which pushes
+// that much of the straight-line body beyond the 64 KB that the instruction cache serves without stalls.
+#ifndef GRID_SINCOS_INLINE
+static __device__ __noinline__ float2 grid_sincos_call(float x) { float s, c; sincosf(x, &s, &c); return make_float2(s, c); }
+static __device__ __noinline__ double2 grid_sincos_call(double x) { double s, c; sincos(x, &s, &c); return make_double2(s, c); }
+__device__ __forceinline__ void grid_sincos(float x, float* s, float* c) { const float2 r = grid_sincos_call(x); *s = r.x; *c = r.y; }
+__device__ __forceinline__ void grid_sincos(double x, double* s, double* c) { const double2 r = grid_sincos_call(x); *s = r.x; *c = r.y; }
+#else
 __device__ __forceinline__ void grid_sincos(float x, float* s, float* c) { sincosf(x, s, c); }
 __device__ __forceinline__ void grid_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+#endif
 
 // ---- pairs of scalars: the dq / dqd derivative columns of a joint go through identical linear maps, so the
 // emitted bodies carry them as one P value.  For T = float P is float2 and every operation below is ONE packed

@@ -23,7 +23,7 @@ CSRC = os.path.join(_PKG, "csrc")
 INCLUDE = os.path.join(_ROOT, "include")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-shared"]
+              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-shared"] + os.environ.get("GRID_NVCC_EXTRA", "").split()
 
 ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
               "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
