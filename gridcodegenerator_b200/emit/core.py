@@ -10,9 +10,12 @@ dot products at run time, helpers/_spatial_algebra_helpers.py:124-143).
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence, Tuple, Union
 
 Number = Union[int, float]
+# a lockstep barrier (GRID_SYNC) at every SYNC_EVERY-th section marker of the emitted bodies (0 = none)
+SYNC_EVERY = int(os.environ.get("GRID_SYNC_EVERY", "8"))
 
 
 class V:
@@ -75,6 +78,7 @@ class Em:
         self.regs_only = False
         self.reg_state: Dict[Tuple, V] = {}
         # emit-time forward-mode AD: 0 = off, 1 = first-order tangents, 2 = also second order
+        self._nsync = 0
         self.ad_order = 0
         self._ad_depth = 0
         self._ad_cap = None
@@ -92,7 +96,9 @@ class Em:
             self.lines.append("GRID_FENCE();")
         # lockstep point: the warps of a CTA re-converge here so that they stream the (straight-line, >100 KB)
         # code through the instruction caches together; a no-op for single-warp CTAs
-        self.lines.append("GRID_SYNC();")
+        self._nsync += 1
+        if SYNC_EVERY > 0 and self._nsync % SYNC_EVERY == 0:
+            self.lines.append("GRID_SYNC();")
 
     def tmp(self, expr: str) -> V:
         name = f"t{self.ctr}"

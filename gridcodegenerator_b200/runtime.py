@@ -64,6 +64,10 @@ def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool
     cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f != "-shared"] + [
         "-c", f"-I{out_dir}", f"-I{INCLUDE}", f'-DGRID_ROBOT_NAME="{name}"', f"-DGRID_PARTS={part}",
         f"-DGRID_DTYPES={dtypes}", os.path.join(CSRC, "grid_capi.cu"), "-o", obj]
+    if part in (0x20, 0x40) and os.environ.get("GRID_SO_PTXAS_O1", "1") == "1":
+        # second-order bodies are ~1 MB of straight-line code: ptxas -O3 needs ~10 min per translation unit on them,
+        # -O1 under 2 min
+        cmd[1:1] = ["-Xptxas", "-O1"]
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
     res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

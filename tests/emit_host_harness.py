@@ -57,7 +57,7 @@ def build_host_inners(robot, workdir=None, second_order=False):
     so = os.path.join(workdir, f"inner_{robot.name}.so")
     with open(cpp, "w") as f:
         f.write(text)
-    subprocess.check_call(["g++", "-O1", "-shared", "-fPIC", "-o", so, cpp])
+    subprocess.check_call(["g++", "-O0", "-shared", "-fPIC", "-o", so, cpp])
     lib = ctypes.CDLL(so)
     return lib, g
 

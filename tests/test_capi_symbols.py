@@ -15,7 +15,7 @@ def _declared():
     return sorted(set(re.findall(r"\b(grid_[a-z0-9_]+)\s*\(", txt)))
 
 
-@pytest.mark.parametrize("name", ["iiwa14"])
+@pytest.mark.parametrize("name", ["pendulum2"])   # smallest robot: the whole library builds in seconds
 def test_library_exports_header_symbols(name):
     from gridcodegenerator_b200.runtime import build_library
     so = build_library(name)
@@ -26,7 +26,7 @@ def test_library_exports_header_symbols(name):
         assert hasattr(lib, sym), f"{sym} declared in grid_b200.h but not exported by {so}"
     lib.grid_robot_name.restype = ctypes.c_char_p
     assert lib.grid_robot_name().decode() == name
-    assert lib.grid_num_joints() == 7
+    assert lib.grid_num_joints() == 2
     assert lib.grid_abi_version() == 4
     assert lib.grid_num_ees() == 1 and lib.grid_has_second_order() == 1
     lib.grid_kernel_info.restype = ctypes.c_long
@@ -41,12 +41,12 @@ def test_no_silent_fallback_without_gpu():
     if torch.cuda.is_available():
         pytest.skip("GPU present")
     from gridcodegenerator_b200.runtime import get_library
-    lib = get_library("iiwa14")
-    x = torch.zeros((4, 21), dtype=torch.float32)
+    lib = get_library("pendulum2")
+    x = torch.zeros((4, 6), dtype=torch.float32)
     with pytest.raises(RuntimeError):
         lib.forward_dynamics_gradient(x)
     # the raw C entry point reports an error code and a message instead of exiting
-    rc = lib.lib.grid_forward_dynamics_gradient_f32(None, 21, None, 4, 9.81, None)
+    rc = lib.lib.grid_forward_dynamics_gradient_f32(None, 6, None, 4, 9.81, None)
     assert rc != 0 and b"grid_forward_dynamics_gradient" in lib.lib.grid_last_error()
 
 
