@@ -188,6 +188,8 @@ ALGO_ORDER = ("end_effector_pose", "end_effector_pose_gradient", "end_effector_p
 def gen_add_includes(self, use_thread_group=False):
     """reference GRiDCodeGenerator.py:66-84; the runtime header is inlined so grid.cuh stays standalone."""
     self._add_block(_sc.INCLUDES)
+    from .emit.core import SYNC_EVERY
+    self.gen_add_code_line(f"#define GRID_LOCKSTEP {int(SYNC_EVERY > 0)}")
     with open(os.path.join(_CSRC, "grid_b200_runtime.cuh")) as f:
         rt = f.read().replace("#pragma once\n", "")
     self._add_block("// ---- inlined gridcodegenerator_b200/csrc/grid_b200_runtime.cuh ----\n" + rt)
