@@ -202,17 +202,20 @@ def gen_add_gpu_err(self):
 
 
 def _scratch_constants(self):
+    """Elements of global scratch per CTA, max over algorithms: per-thread state that does not fit shared memory
+    plus the lane-interleaved output scratch of the transposed-store mode (STAGED = 3)."""
     per4 = per8 = 0
     for name, sp in self._specs.items():
         b = self._body(name)
         IN = [e for _, e in sp.streams]
+        out = sp.out_n(self.model.n)
         for size in (4, 8):
-            NT, state_smem, _ = _hdr.choose_config(max(b.nslots, 1), IN, sp.out_n(self.model.n), size)
-            if not state_smem:
-                if size == 4:
-                    per4 = max(per4, NT * b.nslots)
-                else:
-                    per8 = max(per8, NT * b.nslots)
+            NT, state_smem, staged = _hdr.choose_config(max(b.nslots, 1), IN, out, size)
+            need = (0 if state_smem else NT * max(b.nslots, 1)) + (NT * out if staged == 3 else 0)
+            if size == 4:
+                per4 = max(per4, need)
+            else:
+                per8 = max(per8, need)
     return per4, per8
 
 

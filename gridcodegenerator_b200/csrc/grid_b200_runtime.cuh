@@ -51,11 +51,19 @@ template <> __device__ __forceinline__ float2 mkp<float>(float a, float b) { ret
 template <> __device__ __forceinline__ double_pair mkp<double>(double a, double b) { double_pair r; r.x = a; r.y = b; return r; }
 template <typename T> __device__ __forceinline__ pair_t<T> pbc(T s) { return mkp<T>(s, s); }
 
+#ifdef GRID_PAIR_SCALAR   // A/B switch: the two halves as independent scalar FP32 operations (interleaved chains)
+__device__ __forceinline__ float2 pfma(float2 a, float s, float2 c) { return make_float2(fmaf(a.x, s, c.x), fmaf(a.y, s, c.y)); }
+__device__ __forceinline__ float2 pmul(float2 a, float s) { return make_float2(a.x * s, a.y * s); }
+__device__ __forceinline__ float2 padd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 psub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 padds(float2 a, float s) { return make_float2(a.x + s, a.y + s); }
+#else
 __device__ __forceinline__ float2 pfma(float2 a, float s, float2 c) { return __ffma2_rn(a, make_float2(s, s), c); }
 __device__ __forceinline__ float2 pmul(float2 a, float s) { return __fmul2_rn(a, make_float2(s, s)); }
 __device__ __forceinline__ float2 padd(float2 a, float2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ float2 psub(float2 a, float2 b) { return __ffma2_rn(b, make_float2(-1.0f, -1.0f), a); }
 __device__ __forceinline__ float2 padds(float2 a, float s) { return __fadd2_rn(a, make_float2(s, s)); }
+#endif
 __device__ __forceinline__ float2 pneg(float2 a) { return make_float2(-a.x, -a.y); }
 
 __device__ __forceinline__ double_pair pfma(double_pair a, double s, double_pair c) { double_pair r; r.x = fma(a.x, s, c.x); r.y = fma(a.y, s, c.y); return r; }
@@ -122,6 +130,7 @@ template <class A, typename T, int NT, bool STATE_SMEM, int STAGED>
 constexpr size_t tile_smem_bytes() {
     size_t state = STATE_SMEM ? align16(size_t(A::SLOTS) * NT * sizeof(T)) : 0;
     size_t per_warp = 0;
+    if (STAGED == 3) return state + size_t(TILE) * 33 * sizeof(T) * (NT / 32) + 16;   // one transpose tile per warp
     if (STAGED) {
         for (int s = 0; s < MAX_STREAMS; s++) per_warp += STAGED * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
         per_warp += align16(size_t(TILE) * A::OUT * sizeof(T));
@@ -141,19 +150,43 @@ constexpr size_t tile_smem_bytes() {
 #ifndef GRID_LOCKSTEP
 #define GRID_LOCKSTEP 1
 #endif
+// Only the warps that own a tile in the current round run the body; they meet at named barrier 1 with a thread
+// count that tile_loop publishes per round (warps without a tile skip the round entirely: no dummy arithmetic,
+// stores or spills -- this matters for small batches, where most warps of the persistent grid have no tile).
+__device__ __forceinline__ int& sync_threads_ref() { __shared__ int n; return n; }
 template <int NT>
 __device__ __forceinline__ void cta_sync() {
-    if (NT > 32) asm volatile("bar.sync 0;" ::: );
+    if (NT > 32) {
+        const int n = *reinterpret_cast<volatile int*>(&sync_threads_ref());
+        asm volatile("bar.sync 1, %0;" ::"r"(n));
+    }
+}
+// called by every warp of the CTA at the top of a round; returns whether this warp has a tile
+template <int NT>
+__device__ __forceinline__ bool round_begin(int tile_of_warp0, int stride_w, int num_tiles, int warp) {
+    if (NT > 32 && GRID_LOCKSTEP) {
+        // tiles of warps 0..NWARPS-1 in this round are tile_of_warp0 + w*stride_w (increasing): count the valid ones
+        int nact = 0;
+        if (tile_of_warp0 < num_tiles) nact = min(NT / 32, (num_tiles - 1 - tile_of_warp0) / stride_w + 1);
+        __syncthreads();                        // previous round's barrier-1 users are done with the old count
+        if (threadIdx.x == 0) sync_threads_ref() = nact * 32;
+        __syncthreads();
+        return warp < nact;
+    }
+    return tile_of_warp0 + warp * stride_w < num_tiles;
 }
 #define GRID_SYNC() grid_rt::cta_sync<NT>()
 
 // A CTA of NT threads (NT/32 warps) walks the batch in rounds; in each round warp w of CTA b owns tile
-// (round*(NT/32) + w)*gridDim.x + b (32 knot points, one per lane).  All warps of the CTA execute every
-// round, with dummy work when their tile does not exist, because the body contains CTA-wide lockstep barriers.
+// (round*(NT/32) + w)*gridDim.x + b (32 knot points, one per lane).  Warps without a tile in a round skip it; the
+// lockstep barriers inside the body count only the warps that run (round_begin / cta_sync).
 // The kernel must be launched with exactly NT threads per block.
 // STAGED: 0 = plain loads / stores; 2 = TMA-staged with double-buffered inputs (next tile's load overlaps this
 // tile's math); 1 = TMA-staged with one input buffer (next load issued after the body; frees shared memory for
-// more lockstep warps when the batch fits one or two rounds anyway).
+// more lockstep warps when the batch fits one or two rounds anyway); 3 = transposed store for large per-knot
+// outputs: plain input loads, each lane writes its output row into a lane-interleaved global scratch (element i of
+// lane l at [i*32 + l], one full 128-byte line per store instruction), then the warp copies the scratch into the
+// caller's knot-major rows through a 32 x 33 shared-memory transpose tile (coalesced on both sides).
 template <class A, typename T, int NT, bool STATE_SMEM, int STAGED>
 __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* smem) {
     constexpr int NWARPS = NT / 32;
@@ -173,19 +206,64 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
         S = reinterpret_cast<T*>(smem) + tid;
         off = align16(size_t(A::SLOTS) * NT * sizeof(T));
     } else {
-        S = a.scratch + (size_t(blockIdx.x) * NT) * A::SLOTS + tid;
+        S = a.scratch + size_t(blockIdx.x) * (size_t(NT) * A::SLOTS + (STAGED == 3 ? size_t(NT) * A::OUT : 0)) + tid;
+    }
+
+    if (STAGED == 3) {
+        T* tile_s = reinterpret_cast<T*>(smem + off) + size_t(warp) * TILE * 33;
+        T* scr = a.scratch + size_t(blockIdx.x) * ((STATE_SMEM ? 0 : size_t(NT) * A::SLOTS) + size_t(NT) * A::OUT)
+                 + (STATE_SMEM ? 0 : size_t(NT) * A::SLOTS) + size_t(warp) * TILE * A::OUT;
+        constexpr int NCHUNK = (A::OUT + TILE - 1) / TILE;
+        T* scr0 = scr - size_t(warp) * TILE * A::OUT;          // warp 0's output scratch
+        for (int r = 0; r < rounds; r++) {
+            const int tile0 = blockIdx.x + r * tiles_per_round;  // warp 0's tile; warp w owns tile0 + w*gridDim.x
+            const int nact = tile0 < num_tiles ? min(NWARPS, (num_tiles - 1 - tile0) / int(gridDim.x) + 1) : 0;
+            if (round_begin<NT>(tile0, gridDim.x, num_tiles, warp)) {
+                int k = (first + r * tiles_per_round) * TILE + lane;
+                if (k >= a.num_knots) k = a.num_knots - 1;   // dummy lanes redo the last knot (identical values)
+                const T* x[MAX_STREAMS];
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++)
+                    x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
+                A::template run<NT, TILE>(scr + lane, x[0], x[1], x[2], S, a.gravity);
+            }
+            if (NWARPS > 1) __syncthreads();                 // every active warp's scratch rows are written
+            else __syncwarp();
+            // All warps of the CTA (also those without a tile this round) share the transposition: work item p =
+            // (source warp, chunk of 32 output elements); 32 independent scratch loads (L2 hits) in flight per lane.
+            for (int p = warp; p < nact * NCHUNK; p += NWARPS) {
+                const int ws = p / NCHUNK, i0 = (p - ws * NCHUNK) * TILE;
+                const int tile = tile0 + ws * int(gridDim.x);
+                const int nvalid = min(TILE, a.num_knots - tile * TILE);
+                const T* src = scr0 + size_t(ws) * TILE * A::OUT + size_t(i0) * TILE + lane;
+                T v[TILE];
+#pragma unroll
+                for (int i = 0; i < TILE; i++) v[i] = (i0 + i < A::OUT) ? __ldcg(src + i * TILE) : T(0);
+#pragma unroll
+                for (int i = 0; i < TILE; i++) tile_s[i * 33 + lane] = v[i];
+                __syncwarp();
+                if (i0 + lane < A::OUT) {
+                    T* d = a.out + size_t(tile) * TILE * A::OUT + i0 + lane;
+#pragma unroll 8
+                    for (int l = 0; l < nvalid; l++) d[size_t(l) * A::OUT] = tile_s[lane * 33 + l];
+                }
+                __syncwarp();
+            }
+            if (NWARPS > 1) __syncthreads();                 // scratch rows are free for the next round
+        }
+        return;
     }
 
     if (!STAGED) {
         for (int r = 0; r < rounds; r++) {
             const int tile = first + r * tiles_per_round;
-            if (!GRID_LOCKSTEP && tile >= num_tiles) break;
+            if (!round_begin<NT>(blockIdx.x + r * tiles_per_round, gridDim.x, num_tiles, warp)) continue;
             int k = tile * TILE + lane;
             if (k >= a.num_knots) k = a.num_knots - 1;   // dummy lanes redo the last knot (identical values)
             const T* x[MAX_STREAMS];
 #pragma unroll
             for (int s = 0; s < MAX_STREAMS; s++) x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
-            A::template run<NT>(a.out + size_t(k) * A::OUT, x[0], x[1], x[2], S, a.gravity);
+            A::template run<NT, 1>(a.out + size_t(k) * A::OUT, x[0], x[1], x[2], S, a.gravity);
         }
         return;
     }
@@ -242,7 +320,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
         const int tile = first + r * tiles_per_round;
         const int next = tile + tiles_per_round;
         const bool valid = tile < num_tiles;
-        if (!GRID_LOCKSTEP && !valid) break;
+        if (!round_begin<NT>(blockIdx.x + r * tiles_per_round, gridDim.x, num_tiles, warp)) continue;   // == !valid
         const bool tma = tile_is_tma(tile);
         if (STAGED == 2 && tile_is_tma(next) && lane == 0) issue_load(next, buf ^ 1);
         const int nvalid = valid ? min(TILE, a.num_knots - tile * TILE) : 0;
@@ -269,7 +347,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
             __syncwarp();
             store_pending = false;
         }
-        A::template run<NT>(out_s + lane * A::OUT, x[0], x[1], x[2], S, a.gravity);
+        A::template run<NT, 1>(out_s + lane * A::OUT, x[0], x[1], x[2], S, a.gravity);
         __syncwarp();
         if (STAGED == 1 && tile_is_tma(next)) {      // single input buffer: every lane is done reading it
             fence_proxy_async();
@@ -290,7 +368,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
             __syncwarp();
         }
     }
-    if (lane == 0) bulk_wait0();                     // smem must outlive the last bulk store
+    if (lane == 0) bulk_wait_read0();                // smem must outlive the last bulk store's reads
     __syncwarp();
 }
 

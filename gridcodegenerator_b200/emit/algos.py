@@ -490,8 +490,10 @@ def _halves(em: Em, e):
 
 # ============================================================ kernel bodies
 def _out(em: Em, idx: int, v: V, ptr: str = "o"):
+    """Output element idx of this knot.  OS is the element stride of the output row the body was given: 1 for a
+    row in shared memory / global memory, 32 for the lane-interleaved global scratch of the transposed-store mode."""
     from .core import lit
-    em.line(f"{ptr}[{idx}] = {lit(v.c) if v.is_const else v.s};")
+    em.line(f"{ptr}[{idx}*OS] = {lit(v.c) if v.is_const else v.s};")
 
 
 def _sink_product(em: Em, n: int, c_: int, dc, minv):

@@ -101,7 +101,8 @@ def second_order_enabled(n: int) -> bool:
 
 def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     """(NT, STATE_SMEM, STAGED) for one algorithm and scalar size.  STAGED: 0 = plain loads/stores, 2 = TMA-staged
-    I/O with double-buffered inputs, 1 = TMA-staged with a single input buffer (chosen when that admits more warps).
+    I/O with double-buffered inputs, 1 = TMA-staged with a single input buffer (chosen when that admits more warps),
+    3 = plain loads, outputs through a lane-interleaved global scratch and a shared-memory transposition.
 
     One CTA per SM with as many warps as shared memory (per-thread state + per-warp TMA staging) and the
     register file allow.  The warps of the CTA run in lockstep through the straight-line body (GRID_SYNC points),
@@ -115,11 +116,18 @@ def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
             fit = (SMEM_LIMIT - 16) // (state_w + stage_w)
             if fit >= 1 and (best is None or min(MAX_WARPS, fit) > best[0]):
                 best = (min(MAX_WARPS, fit), nbuf)
-    if best is not None:
+    fit = (SMEM_LIMIT - 16) // (state_w + 32 * 33 * sizeof)
+    if best is not None and (best[0] >= 4 or fit < 2 * best[0] or os.environ.get("GRID_NO_TRANSPOSED") == "1"):
         return 32 * best[0], True, best[1]
-    fit = (SMEM_LIMIT - 16) // state_w
-    if fit >= 1:
-        return 32 * min(MAX_WARPS, fit), True, 0
+    # Staging a large per-knot output (Atlas matrices, second-order tensors) in shared memory would leave 1-3 warps
+    # per SM.  STAGED = 3: every lane writes its output row into a lane-interleaved global scratch (element idx at
+    # [idx*32 + lane]: each store instruction is one full 128-byte line), then the CTA transposes the scratch into
+    # the caller's knot-major rows through 32 x 33 shared-memory tiles with coalesced reads and writes.
+    if fit >= MAX_WARPS_SCRATCH:
+        return 32 * min(MAX_WARPS, fit), True, 3
+    # State too large for >= 4 warps in shared memory (Atlas gradients): state in the global scratch, 4 warps,
+    # plain stores (measured on B200 with tools/tune_config.py: Atlas grad ID 212 us against 271 us transposed and
+    # 294 us with 2 warps of shared-memory state; grad FD 387 / 393 / 662 us; batch 8192).
     return 32 * MAX_WARPS_SCRATCH, False, 0
 
 
@@ -133,7 +141,7 @@ def emit_inner(sp: AlgoSpec, body: algos.Body) -> str:
     doc = (f"/**\n * {body.doc}\n * One thread = one knot point. o: this knot's outputs; inputs: this knot's "
            f"vectors;\n * S: this thread's state base (element i at S[i*NT], {body.nslots} elements).\n"
            f" * Emitted operations (mul+add): {body.n_ops}\n */\n")
-    head = (f"template <typename T, int NT>\n__device__ __forceinline__\n"
+    head = (f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
             f"void {sp.fn}_inner(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n")
     return doc + head + "    using grid_rt::grid_sincos;\n    typedef grid_rt::pair_t<T> P;\n" + body.code + "}\n\n"
 
@@ -143,12 +151,12 @@ def emit_algo_struct(sp: AlgoSpec, body: algos.Body, n: int) -> str:
     args = []
     for (s, off) in sp.split:
         args.append(f"x{s}" + (f" + {off}" if off else ""))
-    call = f"{sp.fn}_inner<T, NT>(o, {', '.join(args)}, S, gravity);"
+    call = f"{sp.fn}_inner<T, NT, OS>(o, {', '.join(args)}, S, gravity);"
     return (f"template <typename T>\nstruct {algo_struct_name(sp)} {{\n"
             f"    static constexpr int IN0 = {IN[0]}, IN1 = {IN[1]}, IN2 = {IN[2]};\n"
             f"    static constexpr int OUT = {sp.out_n(n)};\n"
             f"    static constexpr int SLOTS = {max(body.nslots, 1)};\n"
-            f"    template <int NT>\n"
+            f"    template <int NT, int OS>\n"
             f"    static __device__ __forceinline__ void run(T* __restrict__ o, const T* __restrict__ x0, "
             f"const T* __restrict__ x1, const T* __restrict__ x2, T* __restrict__ S, const T gravity) {{\n"
             f"        {call}\n    }}\n}};\n\n")
@@ -248,7 +256,7 @@ def emit_launch(sp: AlgoSpec, n: int) -> str:
             f"    int blocks = grid_rt::persistent_blocks(reinterpret_cast<const void*>(kern), {C}::NT, "
             f"{C}::SMEM_BYTES, num_timesteps);\n"
             f"    if (blocks <= 0) {{ cudaError_t e = cudaGetLastError(); return e != cudaSuccess ? e : cudaErrorLaunchOutOfResources; }}\n"
-            f"    if (!{C}::STATE_SMEM) {{\n"
+            f"    if (!{C}::STATE_SMEM || {C}::STAGED == 3) {{\n"
             f"        const int cap = grid_rt::scratch_capacity(GRID_SCRATCH_BLOCKS_PER_SM);\n"
             f"        if (cap <= 0 || d_robotModel == nullptr) return cudaErrorInvalidValue;\n"
             f"        if (blocks > cap) blocks = cap;\n"
