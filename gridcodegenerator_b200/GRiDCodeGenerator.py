@@ -157,8 +157,8 @@ def _bind(key: str):
 
 
 for _key in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-             "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so", "end_effector_pose",
-             "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
+             "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so",
+             "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
     _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner_temp_mem_size", _t)
     setattr(GRiDCodeGenerator, f"gen_{_key}_inner", _i)
@@ -182,7 +182,7 @@ from .emit import scaffold as _sc  # noqa: E402
 
 ALGO_ORDER = ("end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian",
               "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-              "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so")
+              "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so")
 
 
 def gen_add_includes(self, use_thread_group=False):
@@ -265,7 +265,7 @@ def gen_all_code(self, use_thread_group=False, include_base_inertia=False, inclu
              "    __host__   gridData<T> *hd_data = init_gridData<T,NUM_TIMESTEPS>();",
              "    __host__   close_grid<T>(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> *hd_data)",
              "  per ALGORITHM in {inverse_dynamics, direct_minv, forward_dynamics, inverse_dynamics_gradient,",
-             "                    forward_dynamics_gradient, aba, crba, idsva_so, fdsva_so}:",
+             "                    forward_dynamics_gradient, forward_dynamics_linearization, aba, crba, idsva_so, fdsva_so}:",
              "    __device__ ALGORITHM_inner<T,NT>(T *o, const T *q, ..., T *S, const T gravity)   one thread = one knot point",
              "    __device__ ALGORITHM_device<T>(const grid_rt::TileArgs<T> &a, unsigned char *s_mem) one warp = 32 knot points",
              "    __global__ ALGORITHM_kernel<T>(T *d_out, const T *d_in, const int stride, ..., const robotModel<T> *, const T gravity, const int NUM_TIMESTEPS)",

@@ -13,6 +13,10 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
+#ifndef GRID_PDL_DEFAULT
+#define GRID_PDL_DEFAULT 0
+#endif
 
 // compiler-only memory fence used by the emitted bodies at joint / column boundaries
 #define GRID_FENCE() asm volatile("" ::"l"(S) : "memory")
@@ -110,6 +114,15 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Programmatic dependent launch (PDL).  The kernels here are short (5-30 us), so the launch latency and the
+// prologue (shared-memory init, mbarrier init) of kernel i+1 are worth hiding behind kernel i.  Every tile kernel
+// releases its dependents at once (pdl_release) and blocks at pdl_wait before its first global-memory access;
+// griddepcontrol.wait returns only when every prerequisite grid has completed and its writes are visible, so
+// stream order semantics are unchanged.  Both are no-ops when the kernel was launched without the attribute
+// (GRID_PDL=0 in the environment, or a plain <<<>>> launch of X_kernel by user code).
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <typename T>
 struct TileArgs {
     const T* in[MAX_STREAMS];   // device arrays, knot-major
@@ -199,6 +212,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     // warp w of CTA b owns tiles (r*NWARPS + w)*gridDim.x + b: the tiles of the last, partial round spread evenly
     // over the SMs (every SM keeps ~the same number of busy warps) instead of leaving whole SMs idle
     const int first = warp * gridDim.x + blockIdx.x;
+    pdl_release();
 
     T* S;
     size_t off = 0;
@@ -209,6 +223,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
         S = a.scratch + size_t(blockIdx.x) * (size_t(NT) * A::SLOTS + (STAGED == 3 ? size_t(NT) * A::OUT : 0)) + tid;
     }
 
+    if (STAGED == 0 || STAGED == 3) pdl_wait();     // the staged path waits after its shared-memory prologue
     if (STAGED == 3) {
         T* tile_s = reinterpret_cast<T*>(smem + off) + size_t(warp) * TILE * 33;
         T* scr = a.scratch + size_t(blockIdx.x) * ((STATE_SMEM ? 0 : size_t(NT) * A::SLOTS) + size_t(NT) * A::OUT)
@@ -297,6 +312,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
     __syncwarp();
+    pdl_wait();                                      // first global access (TMA load / plain load) is below
 
     auto issue_load = [&](int tile, int buf) {      // lane 0 only
         uint32_t bytes = 0;
@@ -405,6 +421,23 @@ static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
     (void)threads;
     const int cap = plan->blocks_per_sm * plan->sms;
     return want < cap ? want : cap;
+}
+
+// Launch with the programmatic-stream-serialization attribute unless GRID_PDL=0 (see pdl_release / pdl_wait).
+static bool pdl_enabled() {
+    static const int on = [] { const char* v = getenv("GRID_PDL"); return (v && *v) ? atoi(v) : GRID_PDL_DEFAULT; }();
+    return on != 0;
+}
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_tile_kernel(void (*kern)(KArgs...), int blocks, int threads, size_t smem, cudaStream_t stream,
+                                      Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
 // Number of CTAs the global state scratch attached to a robot model serves on the current device: a pure function

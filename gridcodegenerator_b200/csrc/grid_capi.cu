@@ -9,6 +9,7 @@
 #include "grid.cuh"
 #include "grid_b200.h"
 
+#include <cstdlib>
 #include <mutex>
 #include <string>
 
@@ -23,8 +24,9 @@
 #define PART_IDSVA 0x20
 #define PART_FDSVA 0x40
 #define PART_EE 0x80
+#define PART_FD_LIN 0x100
 #ifndef GRID_PARTS
-#define GRID_PARTS 0xFF
+#define GRID_PARTS 0x1FF
 #endif
 #ifndef GRID_DTYPES
 #define GRID_DTYPES 3
@@ -135,17 +137,44 @@ int bad_arg(const char* where, const char* what) {
     if (!m) return bad_arg(fn, "no CUDA device");                                       \
     cudaStream_t st = static_cast<cudaStream_t>(s); (void)st
 
-// ---- host-buffer pipeline: chunks of the batch rotate over three streams so that the H2D copy of
-// chunk i+1, the kernel of chunk i and the D2H copy of chunk i-1 overlap (PCIe is full duplex).
+// ---- host-buffer entry points.  Two transports, chosen per call:
+//  * pipeline (default for pageable or unmapped buffers): chunks of the batch rotate over three streams so that
+//    the H2D copy of chunk i+1, the kernel of chunk i and the D2H copy of chunk i-1 overlap (PCIe is full duplex);
+//  * zero-copy (GRID_HOST_ZEROCOPY=1, both buffers pinned and mapped into the device address space, which is what
+//    cudaHostAlloc / torch pin_memory() give under UVA): ONE kernel launch whose TMA tile loads read the caller's
+//    host batch and whose bulk stores write the caller's host result directly over PCIe -- no staging buffers,
+//    no copy-engine hand-offs; the double-buffered tile loop overlaps the two PCIe directions by itself.
+inline int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+inline void* mapped_device_pointer(const void* h) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
 template <typename T, class Launch>
 int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int out_per_knot, int nk, Launch launch) {
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
     HostWork& w = grid_capi_host_work;
     std::lock_guard<std::mutex> lk(w.mu);
-    cudaError_t e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), 0, size_t(nk) * out_per_knot * sizeof(T));
+    cudaError_t e;
+    static const int zero_copy = env_int("GRID_HOST_ZEROCOPY", 0);
+    if (zero_copy) {
+        T* m_in = static_cast<T*>(mapped_device_pointer(h_in));
+        T* m_out = static_cast<T*>(mapped_device_pointer(h_out));
+        if (m_in && m_out) {
+            if ((e = w.ensure(0, 0, 0)) != cudaSuccess) return fail(e, fn);
+            int rc = launch(m_in, m_out, nk, w.streams[0]);
+            if (rc) return rc;
+            return fail(cudaStreamSynchronize(w.streams[0]), fn);
+        }
+    }
+    e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), 0, size_t(nk) * out_per_knot * sizeof(T));
     if (e != cudaSuccess) return fail(e, fn);
-    const int chunk = 16384;                      // multiple of the 32-knot tile: every chunk stays TMA-aligned
+    // multiple of the 32-knot tile: every chunk stays TMA-aligned
+    static const int chunk = ((env_int("GRID_HOST_CHUNK", 8192) + 31) / 32) * 32;
     T* d_in = static_cast<T*>(w.d_in);
     T* d_out = static_cast<T*>(w.d_out);
     int i = 0;
@@ -183,7 +212,7 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
 // ---- per-part kernel introspection, dispatched from grid_kernel_info (defined in the core f32 part)
 #define DECL_INFO(NAME) HIDDEN long grid_capi_info_##NAME##_f32(int algo, int what); \
                         HIDDEN long grid_capi_info_##NAME##_f64(int algo, int what);
-DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(aba_crba) DECL_INFO(idsva) DECL_INFO(fdsva) DECL_INFO(ee)
+DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(aba_crba) DECL_INFO(idsva) DECL_INFO(fdsva) DECL_INFO(ee) DECL_INFO(fd_lin)
 
 // Everything below is instantiated for the dtypes of this translation unit through GRID_FOR_DTYPES(X):
 #if (GRID_DTYPES & 1) && (GRID_DTYPES & 2)
@@ -246,7 +275,7 @@ int grid_num_joints(void) { return N; }
 int grid_num_ees(void) { return grid::NUM_EES; }
 const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
 const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
-int grid_abi_version(void) { return 4; }
+int grid_abi_version(void) { return 5; }
 int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
 int grid_has_ee_hessian(void) { return GRID_HAS_EE_HESSIAN; }
 long grid_kernel_info(int algo, int is_f64, int what) {
@@ -260,6 +289,7 @@ long grid_kernel_info(int algo, int is_f64, int what) {
         case 10: DISPATCH(idsva)
         case 11: DISPATCH(fdsva)
         case 12: case 13: case 14: DISPATCH(ee)
+        case 15: DISPATCH(fd_lin)
     }
     return -1;
 }
@@ -354,6 +384,34 @@ long info_fd_du(int algo, int what) {
             [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
                 return forward_dynamics_gradient_impl<T>(di, 3 * N, dout, c, g, st); }); }
 GRID_FOR_DTYPES(X_FD_DU)
+#endif
+
+// =============================================================== grad FD + Minv + qdd
+#if HAS(PART_FD_LIN)
+namespace {
+template <typename T>
+int forward_dynamics_linearization_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_forward_dynamics_linearization", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));
+    return fail(grid::forward_dynamics_linearization_launch<T>(d_out, d_in, stride, m, g, nk, st), fn);
+}
+template <typename T>
+long info_fd_lin(int algo, int what) {
+    using namespace grid;
+    using RM = const robotModel<T>*;
+    if (algo == 15) GRID_INFO(forward_dynamics_linearization_cfg, forward_dynamics_linearization_algo,
+                              static_cast<void (*)(T*, const T*, const int, RM, const T, const int)>(forward_dynamics_linearization_kernel<T>))
+    return -1;
+}
+}  // namespace
+#define X_FD_LIN(SUF, T)                                                                                           \
+    long grid_capi_info_fd_lin_##SUF(int algo, int what) { return info_fd_lin<T>(algo, what); }                    \
+    extern "C" int grid_forward_dynamics_linearization_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {     \
+        return forward_dynamics_linearization_impl<T>(a, st, o, nk, g, s); }                                       \
+    extern "C" int grid_forward_dynamics_linearization_host_##SUF(const T* h_in, T* h_out, int nk, T g) {          \
+        return host_pipeline<T>("grid_forward_dynamics_linearization_host", h_in, 3 * N, h_out, 3 * N * N + N, nk, \
+            [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
+                return forward_dynamics_linearization_impl<T>(di, 3 * N, dout, c, g, st); }); }
+GRID_FOR_DTYPES(X_FD_LIN)
 #endif
 
 #if HAS(PART_FD_DU_QM)

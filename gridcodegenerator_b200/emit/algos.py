@@ -629,7 +629,11 @@ def fdgrad_solver_policy() -> str:
     return os.environ.get("GRID_FDGRAD_SOLVER", "ltdl")
 
 
-def body_forward_dynamics_gradient(model: Model) -> Body:
+def body_forward_dynamics_gradient(model: Model, linearization: bool = False) -> Body:
+    """grad FD.  With `linearization` the same pass also writes M^-1 (= dqdd/du) and qdd behind the gradient:
+    o = [dqdd/dq | dqdd/dqd | Minv | qdd], 3 n^2 + n elements -- the (A, B, f) triple an MPC / DDP caller needs
+    from one launch.  The reference attempts the Minv side output inside its grad FD body
+    (algorithms/_forward_dynamics_gradient.py:56-59) without a barrier."""
     cx = Ctx(model)
     em, n = cx.em, model.n
     cx.prologue()
@@ -654,6 +658,19 @@ def body_forward_dynamics_gradient(model: Model) -> Body:
         for i_, v_ in enumerate(Dinv):
             em.store(("Dinv2", i_, 0), v_)
         qdd = ltdl_solve(cx, L, Dinv, [em.sub(u[j], c[j]) for j in range(n)])
+    if linearization:
+        em.comment("---- side outputs: Minv (dense symmetric, column-major) and qdd")
+        if fdgrad_solver_policy() == "minv":
+            cols = [[minv_get(Minv, r, k) for r in range(n)] for k in range(n)]
+        else:
+            # column k of M^-1 = solve against unit vector k; structural zeros of the sparse right-hand side fold away
+            cols = [ltdl_solve(cx, L, Dinv, [ONE if r == k else ZERO for r in range(n)]) for k in range(n)]
+        for k in range(n):
+            for r in range(n):
+                # one value per symmetric pair, so that the stored matrix is exactly symmetric
+                _out(em, (2 * n + k) * n + r, cols[k][r] if r <= k else cols[r][k])
+        for j in range(n):
+            _out(em, 3 * n * n + j, qdd[j])
     em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
     rnea_forward(cx, qd, qdd, keep=True)
     rnea_backward(cx, qd, keep_f=True)
@@ -679,7 +696,14 @@ def body_forward_dynamics_gradient(model: Model) -> Body:
                     _out(em, (h * n + c_) * n + r, x[r])
 
     rnea_grad_columns(cx, qd, sink)
+    if linearization:
+        return Body("forward_dynamics_linearization_inner", "", cx,
+                    "[dqdd/dq | dqdd/dqd | Minv | qdd]: grad FD with its Minv and qdd by-products")
     return Body("forward_dynamics_gradient_inner", "", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]")
+
+
+def body_forward_dynamics_linearization(model: Model) -> Body:
+    return body_forward_dynamics_gradient(model, linearization=True)
 
 
 def body_forward_dynamics_gradient_qdd_minv(model: Model) -> Body:

@@ -72,6 +72,11 @@ def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
                  algos.body_forward_dynamics_gradient_qdd_minv,
                  ["q", "qd", "qdd", "Minv"], [("d_q_qd", 2 * n), ("d_qdd", n), ("d_Minv", n * n)],
                  [(0, 0), (0, n), (1, 0), (2, 0)], "d_df_du", lambda n: 2 * n * n),
+        # grad FD + its Minv and qdd by-products in one launch (what an MPC / DDP caller consumes)
+        AlgoSpec("forward_dynamics_linearization", "forward_dynamics_linearization", "FD_LIN", "",
+                 algos.body_forward_dynamics_linearization,
+                 ["q", "qd", "u"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_fd_lin",
+                 lambda n: 3 * n * n + n),
         AlgoSpec("aba", "aba", "ABA", "", algos.body_aba,
                  ["q", "qd", "u"], [("d_q_qd_tau", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_qdd", lambda n: n),
         AlgoSpec("crba", "crba", "CRBA", "", algos.body_crba,
@@ -261,8 +266,8 @@ def emit_launch(sp: AlgoSpec, n: int) -> str:
             f"        if (cap <= 0 || d_robotModel == nullptr) return cudaErrorInvalidValue;\n"
             f"        if (blocks > cap) blocks = cap;\n"
             f"    }}\n"
-            f"    kern<<<blocks, {C}::NT, {C}::SMEM_BYTES, stream>>>({', '.join(call)});\n"
-            f"    return cudaGetLastError();\n}}\n\n")
+            f"    cudaError_t le = grid_rt::launch_tile_kernel(kern, blocks, {C}::NT, {C}::SMEM_BYTES, stream, {', '.join(call)});\n"
+            f"    return le != cudaSuccess ? le : cudaGetLastError();\n}}\n\n")
 
 
 def _sig_types(sp: AlgoSpec) -> str:
@@ -332,6 +337,10 @@ def host_specs(n: int) -> List[HostSpec]:
                  ["if (USE_QDD_MINV_FLAG) err = forward_dynamics_gradient_qdd_minv_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, hd_data->d_qdd, hd_data->d_Minv, d_robotModel, gravity, num_timesteps, 0);",
                   "else err = forward_dynamics_gradient_launch<T>(hd_data->d_df_du, hd_data->d_q_qd_u, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],
                  ("hd_data->d_df_du", "hd_data->h_df_du", "2*NUM_JOINTS*NUM_JOINTS")),
+        HostSpec("forward_dynamics_linearization", "", "FD_LIN", True, ["const int stride_q_qd_u = 3*NUM_JOINTS;"],
+                 [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd_u")],
+                 ["err = forward_dynamics_linearization_launch<T>(hd_data->d_fd_lin, hd_data->d_q_qd_u, stride_q_qd_u, d_robotModel, gravity, num_timesteps, 0);"],
+                 ("hd_data->d_fd_lin", "hd_data->h_fd_lin", "(3*NUM_JOINTS*NUM_JOINTS + NUM_JOINTS)")),
         HostSpec("aba", "", "ABA", True, ["const int stride_q_qd = 3*NUM_JOINTS;"],
                  [("", "hd_data->d_q_qd_u", "hd_data->h_q_qd_u", "stride_q_qd")],
                  ["err = aba_launch<T>(hd_data->d_qdd, hd_data->d_q_qd_u, stride_q_qd, d_robotModel, gravity, num_timesteps, 0);"],

@@ -72,6 +72,7 @@ struct gridData {
     T *d_M;
     T *d_dc_du;
     T *d_df_du;
+    T *d_fd_lin;     // [df_du | Minv | qdd], 3 n^2 + n per knot (forward_dynamics_linearization)
     T *d_eePos;
     T *d_deePos;
     T *d_d2eePos;
@@ -84,6 +85,7 @@ struct gridData {
     T *h_M;
     T *h_dc_du;
     T *h_df_du;
+    T *h_fd_lin;
     T *h_eePos;
     T *h_deePos;
     T *h_d2eePos;
@@ -130,6 +132,7 @@ gridData<T> *init_gridData(const int num_timesteps){
     gpuErrchk(cudaMalloc((void**)&hd_data->d_M, n*n*N*sizeof(T)));
     gpuErrchk(cudaMalloc((void**)&hd_data->d_dc_du, 2*n*n*N*sizeof(T)));
     gpuErrchk(cudaMalloc((void**)&hd_data->d_df_du, 2*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_fd_lin, (3*n*n + n)*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_q_qd_u, 3*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_q_qd, 2*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_q, n*N*sizeof(T)));
@@ -139,6 +142,7 @@ gridData<T> *init_gridData(const int num_timesteps){
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_M, n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_dc_du, 2*n*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_df_du, 2*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_fd_lin, (3*n*n + n)*N*sizeof(T)));
     gpuErrchk(cudaMalloc((void**)&hd_data->d_eePos, 6*NUM_EES*N*sizeof(T)));
     gpuErrchk(cudaMalloc((void**)&hd_data->d_deePos, 6*NUM_EES*n*N*sizeof(T)));
     gpuErrchk(cudaMalloc((void**)&hd_data->d_d2eePos, 6*NUM_EES*n*n*N*sizeof(T)));
@@ -190,6 +194,7 @@ void close_grid(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> 
         gpuErrchk(cudaFree(hd_data->d_q_qd_u)); gpuErrchk(cudaFree(hd_data->d_q_qd)); gpuErrchk(cudaFree(hd_data->d_q));
         gpuErrchk(cudaFree(hd_data->d_c)); gpuErrchk(cudaFree(hd_data->d_Minv)); gpuErrchk(cudaFree(hd_data->d_qdd));
         gpuErrchk(cudaFree(hd_data->d_M)); gpuErrchk(cudaFree(hd_data->d_dc_du)); gpuErrchk(cudaFree(hd_data->d_df_du));
+        gpuErrchk(cudaFree(hd_data->d_fd_lin)); gpuErrchk(cudaFreeHost(hd_data->h_fd_lin));
         gpuErrchk(cudaFreeHost(hd_data->h_q_qd_u)); gpuErrchk(cudaFreeHost(hd_data->h_q_qd)); gpuErrchk(cudaFreeHost(hd_data->h_q));
         gpuErrchk(cudaFreeHost(hd_data->h_c)); gpuErrchk(cudaFreeHost(hd_data->h_Minv)); gpuErrchk(cudaFreeHost(hd_data->h_qdd));
         gpuErrchk(cudaFreeHost(hd_data->h_M)); gpuErrchk(cudaFreeHost(hd_data->h_dc_du)); gpuErrchk(cudaFreeHost(hd_data->h_df_du));

@@ -28,7 +28,8 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 ALGO_INDEX = {"inverse_dynamics": 0, "inverse_dynamics_qdd": 1, "direct_minv": 2, "forward_dynamics": 3,
               "inverse_dynamics_gradient": 4, "inverse_dynamics_gradient_qdd": 5, "forward_dynamics_gradient": 6,
               "forward_dynamics_gradient_qdd_minv": 7, "aba": 8, "crba": 9, "idsva_so": 10, "fdsva_so": 11, "end_effector_pose": 12,
-              "end_effector_pose_gradient": 13, "end_effector_pose_gradient_hessian": 14}
+              "end_effector_pose_gradient": 13, "end_effector_pose_gradient_hessian": 14,
+              "forward_dynamics_linearization": 15}
 
 
 def _nvcc() -> str:
@@ -56,11 +57,11 @@ def library_path(robot_name: str) -> str:
 
 # translation units of one library: (GRID_PARTS bitmask, GRID_DTYPES) -- see csrc/grid_capi.cu
 CAPI_PARTS = [(0x01, 1), (0x01, 2), (0x02, 1), (0x02, 2), (0x04, 1), (0x04, 2), (0x08, 1), (0x08, 2),
-              (0x10, 1), (0x10, 2), (0x20, 1), (0x20, 2), (0x40, 1), (0x40, 2), (0x80, 3)]
+              (0x10, 1), (0x10, 2), (0x20, 1), (0x20, 2), (0x40, 1), (0x40, 2), (0x80, 3), (0x100, 1), (0x100, 2)]
 
 
 def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool) -> str:
-    obj = os.path.join(out_dir, f"capi_{part:02x}_{dtypes}.o")
+    obj = os.path.join(out_dir, f"capi_{part:03x}_{dtypes}.o")
     cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f != "-shared"] + [
         "-c", f"-I{out_dir}", f"-I{INCLUDE}", f'-DGRID_ROBOT_NAME="{name}"', f"-DGRID_PARTS={part}",
         f"-DGRID_DTYPES={dtypes}", os.path.join(CSRC, "grid_capi.cu"), "-o", obj]
@@ -74,7 +75,7 @@ def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool
     if res.returncode != 0:
         raise RuntimeError(f"nvcc failed for robot {name} part {part:#x}/{dtypes}:\n{res.stdout[-4000:]}")
     if verbose:
-        with open(os.path.join(out_dir, f"ptxas_{part:02x}_{dtypes}.log"), "w") as f:
+        with open(os.path.join(out_dir, f"ptxas_{part:03x}_{dtypes}.log"), "w") as f:
             f.write(res.stdout)
     return obj
 
@@ -148,6 +149,8 @@ class GRiDLibrary:
             getattr(L, f"grid_forward_dynamics_gradient_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_forward_dynamics_gradient_qdd_minv_{suf}").argtypes = [vp, ci, vp, vp, vp, ci, g, vp]
             getattr(L, f"grid_forward_dynamics_gradient_host_{suf}").argtypes = [vp, vp, ci, g]
+            getattr(L, f"grid_forward_dynamics_linearization_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
+            getattr(L, f"grid_forward_dynamics_linearization_host_{suf}").argtypes = [vp, vp, ci, g]
             getattr(L, f"grid_aba_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_crba_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_idsva_so_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
@@ -257,6 +260,20 @@ class GRiDLibrary:
             self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
 
+    def forward_dynamics_linearization(self, q_qd_u, gravity: float = 9.81, out=None, split: bool = False):
+        """grad FD with its by-products in one launch: (B, 3n^2 + n) rows [dqdd/dq | dqdd/dqd | Minv | qdd]
+        (include/grid_b200.h).  With `split`, returns the views (df_du (B, 2n^2), Minv (B, n^2), qdd (B, n))."""
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd_u, 3 * n)
+        suf = self._suf(q_qd_u)
+        out = torch.empty((B, 3 * n * n + n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        with torch.cuda.device(q_qd_u.device):
+            self._check(getattr(self.lib, f"grid_forward_dynamics_linearization_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
+        if split:
+            return out[:, :2 * n * n], out[:, 2 * n * n:3 * n * n], out[:, 3 * n * n:]
+        return out
+
     def forward_dynamics_gradient_qdd_minv(self, q_qd, qdd, Minv, gravity: float = 9.81, out=None):
         import torch
         n = self.n
@@ -352,6 +369,18 @@ class GRiDLibrary:
         if h_out is None:
             h_out = torch.empty((B, 2 * n * n), dtype=h_q_qd_u.dtype, pin_memory=True)
         self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_host_{suf}")(h_q_qd_u.data_ptr(), h_out.data_ptr(), B, gravity))
+        return h_out
+
+    def forward_dynamics_linearization_host(self, h_q_qd_u, h_out=None, gravity: float = 9.81):
+        import torch
+        n = self.n
+        if h_q_qd_u.is_cuda or not h_q_qd_u.is_contiguous() or h_q_qd_u.shape[1] != 3 * n:
+            raise ValueError("expected a contiguous host (B, 3n) tensor")
+        B = h_q_qd_u.shape[0]
+        suf = self._suf(h_q_qd_u)
+        if h_out is None:
+            h_out = torch.empty((B, 3 * n * n + n), dtype=h_q_qd_u.dtype, pin_memory=True)
+        self._check(getattr(self.lib, f"grid_forward_dynamics_linearization_host_{suf}")(h_q_qd_u.data_ptr(), h_out.data_ptr(), B, gravity))
         return h_out
 
     def forward_dynamics_host(self, h_q_qd_u, h_out=None, gravity: float = 9.81):

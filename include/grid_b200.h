@@ -84,6 +84,17 @@ int grid_forward_dynamics_gradient_qdd_minv_f64(const double *d_q_qd, int stride
                                                 const double *d_Minv, double *d_df_du, int num_knots,
                                                 double gravity, void *stream);
 
+/* ---- grad FD together with its by-products, one launch: per knot 3 n^2 + n elements
+ *   d_fd_lin = [dqdd/dq (n x n) | dqdd/dqd (n x n) | Minv = dqdd/du (n x n, dense symmetric) | qdd (n)], column-major
+ * i.e. the (A, B, f) of the linearised dynamics an MPC / DDP caller needs.  The reference attempts the Minv side
+ * output inside its grad FD body without a barrier (algorithms/_forward_dynamics_gradient.py:56-59, racy) and
+ * otherwise needs a second direct_minv / forward_dynamics launch (host tiers _direct_minv.py:455-560,
+ * _forward_dynamics.py:117-230); this entry point replaces that launch sequence. */
+int grid_forward_dynamics_linearization_f32(const float *d_q_qd_u, int stride, float *d_fd_lin, int num_knots,
+                                            float gravity, void *stream);
+int grid_forward_dynamics_linearization_f64(const double *d_q_qd_u, int stride, double *d_fd_lin, int num_knots,
+                                            double gravity, void *stream);
+
 /* ---- forward dynamics by the articulated-body algorithm, qdd n per knot; d_q_qd_tau: [q|qd|tau]
  * replaces aba<T> (algorithms/_aba.py:539-596; kernel :482-537) */
 int grid_aba_f32(const float *d_q_qd_tau, int stride, float *d_qdd, int num_knots, float gravity, void *stream);
@@ -127,9 +138,14 @@ int grid_end_effector_pose_gradient_hessian_f64(const double *d_q, int stride, d
                                                 int num_knots, void *stream);
 
 /* ---- host-buffer entry points (the reference's default host semantics: H2D, kernel, D2H, blocking;
- * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / n out). */
+ * algorithms/_forward_dynamics_gradient.py:217-245).  Dense strides (3n in, 2n^2 / 3n^2+n / n out).
+ * Pinned, device-mapped caller buffers (cudaHostAlloc / cudaHostRegister) can take a zero-copy transport with
+ * GRID_HOST_ZEROCOPY=1 in the environment: one kernel reads and writes the host buffers directly over PCIe;
+ * GRID_HOST_CHUNK sets the pipeline's chunk size in knot points (default 8192). */
 int grid_forward_dynamics_gradient_host_f32(const float *h_q_qd_u, float *h_df_du, int num_knots, float gravity);
 int grid_forward_dynamics_gradient_host_f64(const double *h_q_qd_u, double *h_df_du, int num_knots, double gravity);
+int grid_forward_dynamics_linearization_host_f32(const float *h_q_qd_u, float *h_fd_lin, int num_knots, float gravity);
+int grid_forward_dynamics_linearization_host_f64(const double *h_q_qd_u, double *h_fd_lin, int num_knots, double gravity);
 int grid_forward_dynamics_host_f32(const float *h_q_qd_u, float *h_qdd, int num_knots, float gravity);
 int grid_inverse_dynamics_host_f32(const float *h_q_qd_u, float *h_c, int num_knots, float gravity);
 /* release the cached device workspace of the host entry points and the robot model handles */

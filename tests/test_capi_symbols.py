@@ -27,7 +27,7 @@ def test_library_exports_header_symbols(name):
     lib.grid_robot_name.restype = ctypes.c_char_p
     assert lib.grid_robot_name().decode() == name
     assert lib.grid_num_joints() == 2
-    assert lib.grid_abi_version() == 4
+    assert lib.grid_abi_version() == 5
     assert lib.grid_num_ees() == 1 and lib.grid_has_second_order() == 1
     lib.grid_kernel_info.restype = ctypes.c_long
     smem = lib.grid_kernel_info(6, 0, 0)
@@ -55,8 +55,8 @@ def test_generator_api_surface(tmp_path):
     from gridcodegenerator_b200 import GRiDCodeGenerator, load_robot
     g = GRiDCodeGenerator(load_robot("chain3"), FILE_NAMESPACE="mygrid")
     for algo in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
-                 "forward_dynamics_gradient", "aba", "crba", "idsva_so", "fdsva_so", "end_effector_pose",
-                 "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
+                 "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so",
+                 "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
         for tier in ("_inner", "_device", "_kernel", "_host", ""):
             assert callable(getattr(g, f"gen_{algo}{tier}")), (algo, tier)
         assert getattr(g, f"gen_{algo}_inner_temp_mem_size")() >= 0
@@ -68,6 +68,6 @@ def test_generator_api_surface(tmp_path):
                  "forward_dynamics_gradient_single_timing", "forward_dynamics_gradient_compute_only",
                  "init_robotModel", "init_gridData", "init_grid", "close_grid", "FD_DU_DYNAMIC_SHARED_MEM_COUNT",
                  "NUM_JOINTS = 3", "cp.async.bulk", "aba_kernel", "crba_kernel", "idsva_so_kernel", "fdsva_so_kernel",
-                 "idsva_so_host", "end_effector_pose_kernel", "end_effector_pose_gradient_hessian_kernel",
+                 "idsva_so_host", "end_effector_pose_kernel", "forward_dynamics_linearization_kernel", "d_fd_lin", "end_effector_pose_gradient_hessian_kernel",
                  "__ffma2_rn"):
         assert name in txt, name

@@ -34,6 +34,13 @@ def test_emitted_bodies_match_reference_golden(name, golden, tmp_path):
         assert rel_err([call(lib, gen, "aba", n, q, qd, u)], [qdd_fd]) < 1e-8
         M = call(lib, gen, "crba", n * n, q).reshape(n, n).T
         assert np.abs(M @ Minv - np.eye(n)).max() < 1e-7
+        # grad FD + by-products in one body: [df_du | Minv | qdd], Minv exactly symmetric
+        lin = call(lib, gen, "forward_dynamics_linearization", 3 * n * n + n, q, qd, u)
+        assert rel_err([lin[:2 * n * n]], [cm(g_["df_du"][k])]) < 1e-9
+        assert rel_err([lin[2 * n * n:3 * n * n]], [cm(Minv)]) < 1e-9
+        assert rel_err([lin[3 * n * n:]], [qdd_fd]) < 1e-9
+        Ml = lin[2 * n * n:3 * n * n].reshape(n, n)
+        assert np.array_equal(Ml, Ml.T)
         # qdd+Minv input mode: feeding the FD solution reproduces grad FD
         out = call(lib, gen, "forward_dynamics_gradient_qdd_minv", 2 * n * n, q, qd, qdd_fd, cm(Minv))
         assert rel_err([out], [cm(g_["df_du"][k])]) < 1e-9

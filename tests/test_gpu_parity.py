@@ -100,6 +100,35 @@ def test_fd_grad_vs_oracle_fp32(name, B, torch_cuda):
                    orc.batch_rnea_grad(x64, use_qdd=True)) < TOL32
 
 
+@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("iiwa14", 1000), ("hyq", 515), ("atlas", 70), ("branched6", 33),
+                                    ("slider3", 31)])
+@pytest.mark.parametrize("dtype,tol", [("float32", TOL32), ("float64", TOL64 * 10)])
+def test_fd_linearization_vs_oracle(name, B, dtype, tol, torch_cuda):
+    """grad FD + Minv + qdd from one launch (include/grid_b200.h
+    grid_forward_dynamics_linearization): every block against the pinned oracle functions, the gradient block
+    equal to the stand-alone grad FD kernel, Minv exactly symmetric, host entry point == device one."""
+    torch = torch_cuda
+    lib, orc = _lib(name), _oracle(name)
+    n = lib.n
+    rng = np.random.default_rng(7)
+    x = rng.uniform(-1, 1, (B, 3 * n)).astype(dtype)
+    x64 = x.astype(np.float64)
+    X = torch.from_numpy(x).cuda()
+    out = lib.forward_dynamics_linearization(X)
+    assert out.shape == (B, 3 * n * n + n)
+    df_du, Minv, qdd = lib.forward_dynamics_linearization(X, split=True)
+    f = lambda t: t.cpu().numpy().astype(np.float64)
+    assert rel_err(f(df_du), orc.batch_fd_grad(x64)) < tol
+    assert rel_err(f(Minv), orc.batch_minv(x64)) < tol
+    assert rel_err(f(qdd), orc.batch_fd(x64)) < tol
+    assert rel_err(f(df_du), f(lib.forward_dynamics_gradient(X))) < tol * 1e-2      # same arithmetic, other kernel
+    Mm = Minv.reshape(B, n, n)
+    assert torch.equal(Mm, Mm.transpose(1, 2))
+    h = lib.forward_dynamics_linearization_host(torch.from_numpy(x).pin_memory())
+    assert torch.equal(h, out.cpu())
+    assert lib.forward_dynamics_linearization(X[:0]).shape == (0, 3 * n * n + n)
+
+
 @pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("hyq", 16384), ("atlas", 200), ("branched6", 97), ("slider3", 64)])
 def test_aba_crba_fp32(name, B, torch_cuda):
     """ABA and CRBA (reference algorithms/_aba.py, _crba.py; BASELINE configs 3 and 4).  The reference has no

@@ -18,6 +18,8 @@ CASES = [
     (2, "iiwa14", "inverse_dynamics_gradient", 2, 65536),
     (2, "iiwa14", "direct_minv", 1, 65536),
     (2, "iiwa14", "forward_dynamics", 3, 65536),
+    (2, "iiwa14", "forward_dynamics_gradient", 3, 65536),
+    (2, "iiwa14", "forward_dynamics_linearization", 3, 65536),   # grad FD + Minv + qdd, one launch
     (3, "hyq", "forward_dynamics_gradient", 3, 16384),
     (3, "hyq", "aba", 3, 16384),
     (4, "atlas", "forward_dynamics_gradient", 3, 8192),     # 65536 over 8 GPUs = 8192 per GPU

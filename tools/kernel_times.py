@@ -23,6 +23,7 @@ run("fd", lambda: lib.forward_dynamics(x))
 run("id_du", lambda: lib.inverse_dynamics_gradient(q_qd, qdd))
 run("fd_du", lambda: lib.forward_dynamics_gradient(x))
 run("fd_du_qm", lambda: lib.forward_dynamics_gradient_qdd_minv(q_qd, qdd, Minv))
+run("fd_lin", lambda: lib.forward_dynamics_linearization(x))
 run("aba", lambda: lib.aba(x))
 run("crba", lambda: lib.crba(q))
 if hasattr(lib, "has_ee_hessian"):
@@ -58,5 +59,7 @@ if "--time" in sys.argv:
     timed("id_du", lambda: lib.inverse_dynamics_gradient(q_qd, qdd, out=o_g))
     timed("fd_du", lambda: lib.forward_dynamics_gradient(x, out=o_g))
     timed("fd_du_qm", lambda: lib.forward_dynamics_gradient_qdd_minv(q_qd, qdd, Minv, out=o_g))
+    o_l = torch.empty((B, 3 * n * n + n), dtype=torch.float32, device="cuda")
+    timed("fd_lin", lambda: lib.forward_dynamics_linearization(x, out=o_l))
     timed("aba", lambda: lib.aba(x, out=o_c))
     timed("crba", lambda: lib.crba(q, out=o_m))
