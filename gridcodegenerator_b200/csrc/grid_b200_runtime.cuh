@@ -15,13 +15,16 @@
 #include <stdint.h>
 #include <stdlib.h>
 #ifndef GRID_PDL_DEFAULT
-#define GRID_PDL_DEFAULT 0
+#define GRID_PDL_DEFAULT 1
 #endif
 
 // compiler-only memory fence used by the emitted bodies at joint / column boundaries
 #define GRID_FENCE() asm volatile("" ::"l"(S) : "memory")
+// Emitted once per body before its first output write (see tile_loop: the output staging buffer of a TMA-staged
+// tile is still being read by the previous tile's bulk store when the next body starts; the body's first passes
+// write no output, so the wait is deferred to this point and normally finds the store long finished).
 #ifndef GRID_BEFORE_FIRST_OUTPUT
-#define GRID_BEFORE_FIRST_OUTPUT() do { } while (0)
+#define GRID_BEFORE_FIRST_OUTPUT() grid_rt::output_buffer_acquire()
 #endif
 
 namespace grid_rt {
@@ -122,6 +125,12 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // (GRID_PDL=0 in the environment, or a plain <<<>>> launch of X_kernel by user code).
 __device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// lane 0 issued the previous bulk store of this warp's staging buffer; no-op when no bulk group is outstanding
+__device__ __forceinline__ void output_buffer_acquire() {
+    if ((threadIdx.x & 31) == 0) bulk_wait_read0();
+    __syncwarp();
+}
 
 template <typename T>
 struct TileArgs {
@@ -329,7 +338,6 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
 
     uint32_t phase[2] = {0u, 0u};
     int buf = 0;
-    bool store_pending = false;
     if (tile_is_tma(first) && lane == 0) issue_load(first, 0);
 
     for (int r = 0; r < rounds; r++, buf = (STAGED == 2) ? (buf ^ 1) : 0) {
@@ -358,11 +366,8 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
             }
             __syncwarp();
         }
-        if (store_pending) {                         // out_s is still being read by the previous bulk store
-            if (lane == 0) bulk_wait_read0();
-            __syncwarp();
-            store_pending = false;
-        }
+        // out_s may still be read by the previous tile's bulk store: the body waits for it right before its first
+        // output write (GRID_BEFORE_FIRST_OUTPUT -> output_buffer_acquire), not here
         A::template run<NT, 1>(out_s + lane * A::OUT, x[0], x[1], x[2], S, a.gravity);
         __syncwarp();
         if (STAGED == 1 && tile_is_tma(next)) {      // single input buffer: every lane is done reading it
@@ -377,7 +382,6 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
                 bulk_s2g(a.out + size_t(tile) * TILE * A::OUT, out_s, uint32_t(TILE * A::OUT * sizeof(T)));
                 bulk_commit();
             }
-            store_pending = true;
         } else if (valid) {
             T* dst = a.out + size_t(tile) * TILE * A::OUT;
             for (int i = lane; i < nvalid * A::OUT; i += 32) dst[i] = out_s[i];

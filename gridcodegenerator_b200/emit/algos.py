@@ -435,6 +435,223 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
         sink(c, dc)
 
 
+def column_loop_policy() -> bool:
+    """Emit the derivative-column recursion of grad RNEA as ONE runtime loop over columns (rnea_grad_columns_loop)
+    instead of n unrolled copies (rnea_grad_columns)."""
+    return os.environ.get("GRID_COLUMN_LOOP", "0") != "0"
+
+
+class MVec:
+    """A vector that is assigned inside uniform branches of the column loop: plain C variables when the per-knot
+    state is register-resident (small robots) or `force_regs`, else per-thread state slots."""
+
+    def __init__(self, em: Em, name: str, size: int, force_regs: bool = False):
+        self.em, self.name, self.size = em, name, size
+        self.regs = em.regs_only or force_regs
+        if self.regs:
+            em.line("T " + ", ".join(f"{name}_{k}" for k in range(size)) + ";")
+        else:
+            self.idx = [em.slot("mv", name, k) for k in range(size)]
+
+    def _ref(self, k: int) -> str:
+        return f"{self.name}_{k}" if self.regs else f"{self.em.state_name}[{self.idx[k]}*{self.em.stride_name}]"
+
+    def get(self, k: int) -> V:
+        return self.em.tmp(self._ref(k))          # a copy: later assignments must not change what was read
+
+    def getv(self, lo: int = 0, hi: Optional[int] = None) -> List[V]:
+        return [self.get(k) for k in range(lo, self.size if hi is None else hi)]
+
+    def set(self, k: int, v: V):
+        from .core import lit
+        self.em.line(f"{self._ref(k)} = {lit(v.c) if v.is_const else v.s};")
+
+    def setv(self, vec: Sequence[V], lo: int = 0):
+        for k, v in enumerate(vec):
+            self.set(lo + k, v)
+
+
+def rnea_grad_columns_loop(cx: Ctx, qd: Sequence[V], sink: str):
+    """Same mathematics as rnea_grad_columns, emitted as one runtime loop over the derivative column c_.
+
+    Column c_ touches subtree(c_) going forward and subtree(c_) + ancestors(c_) going backward.  The loop body holds
+    one block per joint for each sweep, guarded by a condition on c_ that is uniform over the CTA (every lane
+    works on the same column), so no lane ever executes a block its column does not need: the executed operation
+    count equals the unrolled form's up to the seed-specific constant folding, while the code shrinks from
+    sum_c |subtree(c)| joint blocks to n.  For iiwa14 grad FD that is ~110 KB -> ~60 KB of SASS, under the 64 KB
+    beyond which ncu shows instruction-fetch stalls doubling the time per instruction (profiles/r01b_noinst_by_address.txt).
+
+    sink: "id"  -- write [dc/dq | dc/dqd] column c_ to o;
+          "fd"  -- -M^-1 dc by the sparse L^T D L solve (factors in the state: ("L", k, i), ("Dinv2", i, 0)), fused into
+                   the sweeps: L^-T during the backward sweep (same support), D^-1, then L^-1 ascending."""
+    em, m, n = cx.em, cx.m, cx.n
+    from .core import lit
+    bits = lambda js: sum(1 << j for j in js)
+    msk = lambda js: f"(({bits(js)}ull >> c_) & 1ull)"
+    last = [max(m.subtree[j]) for j in range(n)]
+    root = [min(m.ancestors[j]) if m.ancestors[j] else j for j in range(n)]
+    nonadj_parent = {p for j, p in enumerate(m.parent) if p >= 0 and p != j - 1}
+    chain_child = [(j + 1 < n and m.parent[j + 1] == j) for j in range(n)]
+    O = lambda col, row: f"o[({col}*{n} + {row})*OS]"
+
+    base_ops = em.n_ops
+    executed = 0
+
+    _acquire_out(em)
+    em.line("#pragma unroll 1")
+    em.line(f"for (int c_ = 0; c_ < {n}; ++c_) {{")
+    F = [MVec(em, f"cF{j}", 12) for j in range(n)]
+    DV = {p: MVec(em, f"cDV{p}", 12) for p in sorted(nonadj_parent)}
+    DA = {p: MVec(em, f"cDA{p}", 12) for p in sorted(nonadj_parent)}
+    cdv, cda = MVec(em, "ccv", 12, force_regs=True), MVec(em, "cca", 12, force_regs=True)
+    if sink == "fd":
+        XA = {j: MVec(em, f"cXA{j}", 2) for j in range(n) if m.children[j]}
+        Y = [MVec(em, f"cY{j}", 2) for j in range(n)]
+        XX = {j: MVec(em, f"cXX{j}", 2) for j in range(n) if m.children[j]}
+        for j in XA:
+            XA[j].setv([ZERO, ZERO])
+
+    def finish_forward(j, jd, v, Iv, dv, da):
+        # dv, da: [q half (6), qd half (6)];  df = dv x* Iv + I da + v x* (I dv)   (reference _test.py:389-424)
+        df = []
+        for h in (0, 1):
+            xv, xa = dv[h], da[h]
+            df += fxv(em, v, inertia_mul(em, jd.I, xv), acc=fxv(em, xv, Iv, acc=inertia_mul(em, jd.I, xa)))
+        F[j].setv(df)
+        if chain_child[j]:
+            cdv.setv(dv[0] + dv[1])
+            cda.setv(da[0] + da[1])
+        if j in nonadj_parent:
+            DV[j].setv(dv[0] + dv[1])
+            DA[j].setv(da[0] + da[1])
+
+    # ---------------------------------------------------------------- forward sweep
+    for j in range(n):
+        jd = m.joints[j]
+        S, p = jd.S, jd.parent
+        t0 = em.n_ops
+        em.line(f"if (c_ == {j}) {{")
+        em.comment(f"grad RNEA column loop: seed at joint {j}")
+        v, Iv, Xa = em.load_vec("v", j), em.load_vec("Iv", j), em.load_vec("Xa", j)
+        dvq = mxS(em, S, v) if p >= 0 else [ZERO] * 6                  # MxXv == Mxv since S x S = 0
+        dvd = unit(S, ONE)
+        daq = [em.add(x, y) for x, y in zip(mxS(em, S, dvq, qd[j]), mxS(em, S, Xa))]
+        dad = mxS(em, S, v)                                            # mxS(S) qd = 0
+        finish_forward(j, jd, v, Iv, [dvq, dvd], [daq, dad])
+        em.line("}")
+        executed += em.n_ops - t0
+        if m.ancestors[j]:
+            t0 = em.n_ops
+            em.line(f"else if {msk(m.ancestors[j])} {{")
+            em.comment(f"grad RNEA column loop: forward joint {j}")
+            v, Iv = em.load_vec("v", j), em.load_vec("Iv", j)
+            if p == j - 1:
+                pdv, pda = cdv.getv(), cda.getv()
+            else:
+                pdv, pda = DV[p].getv(), DA[p].getv()
+            dv, da = [], []
+            for h in (0, 1):
+                xv = cx.X[j].apply(em, pdv[6 * h:6 * h + 6])
+                xa = [em.add(x, y) for x, y in zip(cx.X[j].apply(em, pda[6 * h:6 * h + 6]), mxS(em, S, xv, qd[j]))]
+                dv.append(xv)
+                da.append(xa)
+            finish_forward(j, jd, v, Iv, dv, da)
+            em.line("}")
+            executed += (em.n_ops - t0) * len(m.ancestors[j])
+        if m.children[j]:
+            em.line(f"else if (c_ > {j} && c_ <= {last[j]}) {{")     # strict ancestor of the column's joint
+            F[j].setv([ZERO] * 12)
+            em.line("}")
+
+    # ---------------------------------------------------------------- backward sweep (+ L^-T and D^-1 of the solve)
+    for j in range(n - 1, -1, -1):
+        jd = m.joints[j]
+        S, p = jd.S, jd.parent
+        cond = msk(m.ancestors[j] + [j])
+        ncols = len(m.ancestors[j]) + 1
+        if m.children[j]:
+            cond += f" || (c_ > {j} && c_ <= {last[j]})"
+            ncols += last[j] - j
+        t0 = em.n_ops
+        em.line(f"if ({cond}) {{")
+        em.comment(f"grad RNEA column loop: backward joint {j}")
+        f = F[j].getv()
+        fq, fd_ = f[:6], f[6:]
+        em.line(f"T cdq_ = {fq[S].s}, cdd_ = {fd_[S].s};")
+        special = p >= 0 or jd.damping != 0.0
+        if p >= 0:
+            em.line("T " + ", ".join(f"cg{k}_ = {fq[k].s}" for k in range(6)) + ";")
+        if special:
+            t1 = em.n_ops
+            em.line(f"if (c_ == {j}) {{")
+            if p >= 0:
+                Mxf = mxS(em, S, em.load_vec("f", j))                  # - X^T mxS(f) (reference _test.py:434-437)
+                for k in range(6):
+                    if not Mxf[k].is_zero():
+                        em.line(f"cg{k}_ = cg{k}_ - {lit(Mxf[k].c) if Mxf[k].is_const else Mxf[k].s};")
+                        em.n_ops += 1
+            if jd.damping != 0.0:
+                em.line(f"cdd_ = cdd_ + {lit(jd.damping)};")
+                em.n_ops += 1
+            em.line("}")
+            executed -= (em.n_ops - t1) * (ncols - 1)                  # the special case runs for one column only
+        dcq, dcd = V(s="cdq_"), V(s="cdd_")
+        if p >= 0:
+            gq = [V(s=f"cg{k}_") for k in range(6)]
+            acc = F[p].getv()
+            F[p].setv(cx.X[j].applyT(em, gq, acc=acc[:6]) + cx.X[j].applyT(em, fd_, acc=acc[6:]))
+        if sink == "id":
+            em.line(f"{O('c_', j)} = cdq_; {O(f'({n} + c_)', j)} = cdd_;")
+        else:
+            x = [dcq, dcd]
+            if m.children[j]:
+                xa = XA[j].getv()
+                x = [em.add(dcq, xa[0]), em.add(dcd, xa[1])]
+            for a in m.ancestors[j]:
+                Lja = em.load(("L", j, a))
+                cur = XA[a].getv()
+                XA[a].setv([em.lincomb([(1.0, cur[h]), (-1.0, Lja, x[h])]) for h in (0, 1)])
+            Dj = em.load(("Dinv2", j, 0))
+            Y[j].setv([em.lincomb([(-1.0, x[h], Dj)]) for h in (0, 1)])
+        em.line("}")
+        executed += (em.n_ops - t0) * ncols
+        if ncols < n:
+            if sink == "id":
+                em.line(f"else {{ {O('c_', j)} = T(0); {O(f'({n} + c_)', j)} = T(0); }}")
+            else:
+                em.line("else {")
+                Y[j].setv([ZERO, ZERO])
+                em.line("}")
+
+    # ---------------------------------------------------------------- L^-1 ascending and the output column
+    if sink == "fd":
+        for i in range(n):
+            lo, hi = root[i], last[root[i]]
+            whole = lo == 0 and hi == n - 1
+            t0 = em.n_ops
+            if not whole:
+                em.line(f"if (c_ >= {lo} && c_ <= {hi}) {{")
+            else:
+                em.line("{")
+            y = Y[i].getv()
+            x = []
+            for h in (0, 1):
+                terms = [(1.0, y[h])]
+                for a in m.ancestors[i]:
+                    terms.append((-1.0, em.load(("L", i, a)), XX[a].get(h)))
+                x.append(em.lincomb(terms))
+            if m.children[i]:
+                XX[i].setv(x)
+            from_v = lambda v_: lit(v_.c) if v_.is_const else v_.s
+            em.line(f"{O('c_', i)} = {from_v(x[0])}; {O(f'({n} + c_)', i)} = {from_v(x[1])};")
+            em.line("}")
+            executed += (em.n_ops - t0) * (hi - lo + 1)
+            if not whole:
+                em.line(f"else {{ {O('c_', i)} = T(0); {O(f'({n} + c_)', i)} = T(0); }}")
+    em.line("}")
+    em.n_ops = base_ops + executed          # executed (not static) operation count per knot
+
+
 class _TuplePusher(Pusher):
     """Pusher over (q, qd) tuples of scalars: the unpacked (GRID_EMIT_PAIRS=0) form of a pair column."""
 
@@ -489,10 +706,20 @@ def _halves(em: Em, e):
 
 
 # ============================================================ kernel bodies
+def _acquire_out(em: Em):
+    """Once per body, before its first output write: the tile's output staging buffer may still be read by the
+    previous tile's TMA bulk store; the runtime waits for that here (GRID_BEFORE_FIRST_OUTPUT), i.e. after the
+    passes that produce no output, instead of before the whole body."""
+    if not getattr(em, "_out_acquired", False):
+        em._out_acquired = True
+        em.line("GRID_BEFORE_FIRST_OUTPUT();")
+
+
 def _out(em: Em, idx: int, v: V, ptr: str = "o"):
     """Output element idx of this knot.  OS is the element stride of the output row the body was given: 1 for a
     row in shared memory / global memory, 32 for the lane-interleaved global scratch of the transposed-store mode."""
     from .core import lit
+    _acquire_out(em)
     em.line(f"{ptr}[{idx}*OS] = {lit(v.c) if v.is_const else v.s};")
 
 
@@ -573,7 +800,10 @@ def body_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> Body:
             _out(cx.em, c * n + r, x)
             _out(cx.em, (n + c) * n + r, y)
 
-    rnea_grad_columns(cx, qd, sink)
+    if column_loop_policy():
+        rnea_grad_columns_loop(cx, qd, "id")
+    else:
+        rnea_grad_columns(cx, qd, sink)
     return Body("inverse_dynamics_gradient_inner", "", cx, "[dc/dq | dc/dqd], column-major n x 2n")
 
 
@@ -695,7 +925,10 @@ def body_forward_dynamics_gradient(model: Model, linearization: bool = False) ->
                 for r in range(n):
                     _out(em, (h * n + c_) * n + r, x[r])
 
-    rnea_grad_columns(cx, qd, sink)
+    if column_loop_policy() and fdgrad_solver_policy() != "minv":
+        rnea_grad_columns_loop(cx, qd, "fd")
+    else:
+        rnea_grad_columns(cx, qd, sink)
     if linearization:
         return Body("forward_dynamics_linearization_inner", "", cx,
                     "[dqdd/dq | dqdd/dqd | Minv | qdd]: grad FD with its Minv and qdd by-products")
