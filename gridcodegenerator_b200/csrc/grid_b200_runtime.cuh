@@ -415,6 +415,11 @@ static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem_bytes) != cudaSuccess) return -1;
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
         if (per_sm <= 0) { per_sm = 0; }
+        // GRID_MAX_BLOCKS_PER_SM (environment, tuning): cap on resident CTAs per SM.  Each CTA is one lockstep group,
+        // i.e. one instruction stream; kernels whose straight-line body is far beyond the instruction caches are
+        // bound by the SM's instruction-fetch path, which independent CTAs on one SM have to share.
+        static const int env_cap = [] { const char* v = getenv("GRID_MAX_BLOCKS_PER_SM"); return (v && *v) ? atoi(v) : 0; }();
+        if (env_cap > 0 && per_sm > env_cap) per_sm = env_cap;
         if (ncache >= MAX_PLANS) ncache = 0;         // recycle: a plan is cheap to recompute
         cache[ncache] = KernelPlan{fn, dev, per_sm, sms};
         plan = &cache[ncache++];
