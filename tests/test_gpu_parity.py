@@ -305,3 +305,21 @@ def test_full_size_properties(torch_cuda):
     h_in = torch.from_numpy(x32).pin_memory()
     h_out = lib.forward_dynamics_gradient_host(h_in)
     assert torch.equal(h_out, out.cpu())
+
+
+@pytest.mark.parametrize("env", [{"GRID_HOST_ZEROCOPY": "1"}, {"GRID_HOST_CHUNK": "1000"}, {"GRID_PDL": "0"}])
+def test_host_transports_match_device_path(env, torch_cuda):
+    """The host-buffer entry point's transports (zero-copy over mapped pinned memory, odd chunk sizes) and the
+    launch without programmatic dependent launch are read from the environment once per process, so each runs in
+    a child process (tools/e2e_sweep.py) and must reproduce the device path bit for bit."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ, E2E_BATCH="5000", **env)
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "e2e_sweep.py")], env=e, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["matches_device_path"] is True and line["batch"] == 5000
