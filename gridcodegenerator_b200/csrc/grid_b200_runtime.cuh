@@ -14,6 +14,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
+#ifndef GRID_PDL_PREFETCH
+#define GRID_PDL_PREFETCH 1
+#endif
 #ifndef GRID_PDL_DEFAULT
 #define GRID_PDL_DEFAULT 1
 #endif
@@ -315,6 +318,16 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     for (int s = 0; s < MAX_STREAMS; s++)
         if (in_n<A>(s)) dense = dense && a.stride[s] == in_n<A>(s) && (reinterpret_cast<uintptr_t>(a.in[s]) & 15) == 0;
 
+    // While the previous kernel of the stream is still finishing (programmatic dependent launch), pull this warp's
+    // first input tile into L2: a prefetch moves no data into the SM and L2 is the coherence point, so it is safe
+    // even if that kernel is still writing the buffer; the TMA load after pdl_wait() then hits L2 instead of HBM.
+    if (GRID_PDL_PREFETCH && dense && lane == 0 && first < num_tiles && (first + 1) * TILE <= a.num_knots) {
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++)
+            if (in_n<A>(s))
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.in[s] + size_t(first) * TILE * in_n<A>(s)),
+                             "r"(uint32_t(TILE * in_n<A>(s) * sizeof(T))) : "memory");
+    }
     // dummy lanes / dummy warps read whatever is in the staging buffers: make it finite
     for (size_t i = lane; i < out_off / sizeof(T); i += 32) reinterpret_cast<T*>(wbase)[i] = T(0);
     if (lane == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); }
