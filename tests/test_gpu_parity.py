@@ -323,3 +323,27 @@ def test_host_transports_match_device_path(env, torch_cuda):
     assert r.returncode == 0, r.stderr[-2000:]
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["matches_device_path"] is True and line["batch"] == 5000
+
+
+@pytest.mark.parametrize("name,B", [("iiwa14", 1), ("iiwa14", 33), ("iiwa14", 1000), ("hyq", 97), ("atlas", 40)])
+def test_output_guard_bands(name, B, torch_cuda):
+    """Own bounds check (compute-sanitizer is closed on this pool): every output-writing path (TMA bulk stores,
+    ragged-tail plain stores, transposed stores, global-scratch kernels) writes exactly its (B, m) rows -- guard
+    words placed directly before and after the output rows stay untouched, and the rows equal an unguarded run."""
+    torch = torch_cuda
+    lib = _lib(name)
+    n = lib.n
+    rng = np.random.default_rng(11)
+    x = torch.from_numpy(rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)).cuda()
+    G = 64     # guard elements (256 B: keeps the rows 16-byte aligned so the TMA path is the one exercised)
+    cases = [("forward_dynamics_gradient", x, 2 * n * n), ("forward_dynamics_linearization", x, 3 * n * n + n),
+             ("inverse_dynamics_gradient", x[:, :2 * n].contiguous(), 2 * n * n), ("forward_dynamics", x, n),
+             ("crba", x[:, :n].contiguous(), n * n), ("aba", x, n)]
+    for method, inp, m in cases:
+        buf = torch.full((G + B * m + G,), 12345.0, dtype=torch.float32, device="cuda")
+        out = buf[G:G + B * m].view(B, m)
+        got = getattr(lib, method)(inp, out=out)
+        torch.cuda.synchronize()
+        assert got.data_ptr() == out.data_ptr()
+        assert bool((buf[:G] == 12345.0).all()) and bool((buf[G + B * m:] == 12345.0).all()), method
+        assert torch.equal(out, getattr(lib, method)(inp)), method
