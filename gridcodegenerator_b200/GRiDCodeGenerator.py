@@ -35,6 +35,7 @@ class GRiDCodeGenerator:
             raise NotImplementedError("floating-base robots are out of scope of the B200 hot path (SURVEY.md 2.1 row 18)")
         self.model = Model(robotObj)
         self._bodies: Dict[str, _algos.Body] = {}
+        self._sbodies: Dict[str, _algos.SplitBody] = {}
         self._specs = {sp.fn + sp.tag: sp for sp in _hdr.specs(self.model.n, robotObj.get_total_leaf_nodes())}
 
     # ------------------------------------------------- emission core (L1 API)
@@ -97,6 +98,11 @@ class GRiDCodeGenerator:
             self._add_block(_hdr.emit_inner(sp, b))
             self._add_block(_hdr.emit_algo_struct(sp, b, self.model.n))
             self._add_block(_hdr.emit_config(sp, b, self.model.n))
+            if _hdr.has_split(sp, self.model.n):
+                # second form of the same algorithm: phase A on one warp, derivative columns spread over the CTA's warps
+                if v not in self._sbodies:
+                    self._sbodies[v] = _hdr.split_body(sp, self.model)
+                self._add_block(_hdr.emit_split(sp, self._sbodies[v], self.model.n, b.nslots))
 
     def _gen_device(self, key: str, variants=None):
         # device and kernel tiers are emitted together (the kernel is a 6-line shell around the device tier)

@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <mutex>
 #ifndef GRID_PDL_PREFETCH
 #define GRID_PDL_PREFETCH 1
 #endif
@@ -405,6 +406,142 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
     __syncwarp();
 }
 
+// ------------------------------------------------------------------ split (warp-specialised) tile loop
+// One CTA of A::NW warps owns ONE 32-knot tile at a time (lane = knot in every warp).  Phase A (the first-order
+// passes) runs on A::NA warps -- part p on warp p: the parts are independent pieces of the first-order work, e.g. the
+// base-rooted trees (limbs) of the robot -- and publishes the per-knot state in shared memory as S[slot*32 + lane];
+// after a CTA barrier every warp runs its share of the derivative columns (phase B: A::phaseB switches on the warp
+// index) reading that state, writing the tile's output rows.  Against the one-lane-one-knot loop above this cuts the
+// latency of a tile from the whole body to (longest phase-A part + longest column group) and spreads a tile's
+// instruction stream over several instruction-fetch streams, which is what small batches (one tile per SM or
+// fewer) and big robots (Atlas: 870 KB of straight-line code per tile) need.
+// Shared-memory layout: [state A::SLOTS x 32][inputs, double buffered][output rows 32 x OUT if OUT_STAGED][2 mbarriers].
+template <class A, typename T, bool OUT_STAGED>
+constexpr size_t split_smem_bytes() {
+    size_t b = align16(size_t(A::SLOTS) * TILE * sizeof(T));
+    for (int s = 0; s < MAX_STREAMS; s++) b += 2 * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+    if (OUT_STAGED) b += align16(size_t(TILE) * A::OUT * sizeof(T));
+    return b + 32;
+}
+
+template <class A, typename T, bool OUT_STAGED>
+__device__ __forceinline__ void tile_loop_split(const TileArgs<T>& a, unsigned char* smem) {
+    constexpr int NW = A::NW;
+    constexpr int NT = NW * 32;
+    if (blockDim.x != NT) return;                  // launch contract: exactly NW warps per CTA
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int num_tiles = (a.num_knots + TILE - 1) / TILE;
+    pdl_release();
+
+    T* S = reinterpret_cast<T*>(smem) + lane;
+    size_t off = align16(size_t(A::SLOTS) * TILE * sizeof(T));
+    size_t in_off[MAX_STREAMS][2];
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            in_off[s][b] = off;
+            off += align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+        }
+    const size_t stage_end = off;
+    T* out_s = reinterpret_cast<T*>(smem + off);
+    if (OUT_STAGED) off += align16(size_t(TILE) * A::OUT * sizeof(T));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + off);
+
+    bool dense = (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++)
+        if (in_n<A>(s)) dense = dense && a.stride[s] == in_n<A>(s) && (reinterpret_cast<uintptr_t>(a.in[s]) & 15) == 0;
+
+    const int first = blockIdx.x;
+    if (GRID_PDL_PREFETCH && dense && tid == 0 && first < num_tiles && (first + 1) * TILE <= a.num_knots) {
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++)
+            if (in_n<A>(s))
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.in[s] + size_t(first) * TILE * in_n<A>(s)),
+                             "r"(uint32_t(TILE * in_n<A>(s) * sizeof(T))) : "memory");
+    }
+    // dummy lanes of a ragged tile read whatever is in the input staging buffers: make it finite
+    {
+        T* z = reinterpret_cast<T*>(smem + in_off[0][0]);
+        for (size_t i = tid; i < (stage_end - in_off[0][0]) / sizeof(T); i += NT) z[i] = T(0);
+    }
+    if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+    __syncthreads();
+    pdl_wait();                                      // first global access is below
+
+    auto issue_load = [&](int tile, int buf) {      // thread 0 only
+        uint32_t bytes = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++) bytes += in_n<A>(s) ? uint32_t(TILE * in_n<A>(s) * sizeof(T)) : 0u;
+        mbar_expect_tx(&bar[buf], bytes);
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++)
+            if (in_n<A>(s))
+                bulk_g2s(smem + in_off[s][buf], a.in[s] + size_t(tile) * TILE * in_n<A>(s),
+                         uint32_t(TILE * in_n<A>(s) * sizeof(T)), &bar[buf]);
+    };
+    auto tile_is_tma = [&](int tile) { return dense && tile < num_tiles && (tile + 1) * TILE <= a.num_knots; };
+
+    uint32_t phase[2] = {0u, 0u};
+    int buf = 0;
+    if (tid == 0 && tile_is_tma(first)) issue_load(first, 0);
+
+    for (int tile = first; tile < num_tiles; tile += gridDim.x, buf ^= 1) {
+        const int next = tile + gridDim.x;
+        const bool tma = tile_is_tma(tile);
+        const int nvalid = min(TILE, a.num_knots - tile * TILE);
+        if (tid == 0 && tile_is_tma(next)) issue_load(next, buf ^ 1);   // buf^1 was last read two barriers ago
+        if (A::PHASE_A_WRITES && OUT_STAGED) {                // phase A writes output rows too (side outputs)
+            if (tid == 0) bulk_wait_read0();
+            __syncthreads();
+        }
+        int k = tile * TILE + lane;
+        if (k >= a.num_knots) k = a.num_knots - 1;           // dummy lanes of a ragged tile redo its last knot
+        T* o = OUT_STAGED ? out_s + size_t(lane) * A::OUT : a.out + size_t(k) * A::OUT;
+        if (warp < A::NA) {
+            const T* x[MAX_STREAMS];
+            if (tma) {
+                mbar_wait(&bar[buf], phase[buf]);
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++)
+                    x[s] = reinterpret_cast<const T*>(smem + in_off[s][buf]) + lane * in_n<A>(s);
+            } else {                                          // ragged tail / strided or unaligned caller buffers
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++)
+                    x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
+            }
+            A::template phaseA<TILE, 1>(warp, o, x[0], x[1], x[2], S, a.gravity);
+        }
+        if (tma) phase[buf] ^= 1u;
+        // the output rows may still be read by the previous tile's bulk store (issued by thread 0)
+        if (OUT_STAGED && tid == 0) bulk_wait_read0();
+        __syncthreads();                                      // state published, output rows free
+        A::template phaseB<TILE, 1>(warp, o, S);
+        if (OUT_STAGED) {
+            fence_proxy_async();
+            __syncthreads();                                  // all columns written; state free for the next tile
+            if (tma) {
+                if (tid == 0) {
+                    bulk_s2g(a.out + size_t(tile) * TILE * A::OUT, out_s, uint32_t(TILE * A::OUT * sizeof(T)));
+                    bulk_commit();
+                }
+            } else {
+                T* dst = a.out + size_t(tile) * TILE * A::OUT;
+                for (int i = tid; i < nvalid * A::OUT; i += NT) dst[i] = out_s[i];
+                __syncthreads();                              // out_s is rewritten by the next tile's phase A
+            }
+        } else {
+            __syncthreads();
+        }
+    }
+    if (OUT_STAGED && tid == 0) bulk_wait_read0();   // smem must outlive the last bulk store's reads
+    __syncthreads();
+}
+
 // ------------------------------------------------------------------ host side
 struct KernelPlan { const void* fn; int device; int blocks_per_sm; int sms; };
 
@@ -417,8 +554,10 @@ static int persistent_blocks(const void* fn, int threads, size_t smem_bytes, int
     constexpr int MAX_PLANS = 256;
     static KernelPlan cache[MAX_PLANS];
     static int ncache = 0;
+    static std::mutex mu;                    // the C ABI is callable from several host threads (one per device)
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    std::lock_guard<std::mutex> lk(mu);
     const KernelPlan* plan = nullptr;
     for (int i = 0; i < ncache; i++)
         if (cache[i].fn == fn && cache[i].device == dev) { plan = &cache[i]; break; }
@@ -460,6 +599,22 @@ static cudaError_t launch_tile_kernel(void (*kern)(KArgs...), int blocks, int th
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// Which form of a kernel a launcher uses when the algorithm has both: GRID_SPLIT_MODE=0 never the split form,
+// =1 always, otherwise the split form for batches of at most `max_knots` knot points (the latency-bound regime:
+// too few tiles to give every SM's schedulers a warp; the emitted <algo>_split_max_knots() gives the default,
+// GRID_SPLIT_MAX_KNOTS overrides it).
+// The environment is read at every launch (two getenv calls, ~0.1 us) so that a process can switch forms, e.g.
+// tests comparing the two.
+static bool use_split_kernel(int num_knots, int max_knots) {
+    const char* v = getenv("GRID_SPLIT_MODE");
+    const int mode = (v && *v) ? atoi(v) : -1;
+    v = getenv("GRID_SPLIT_MAX_KNOTS");
+    const int env_max = (v && *v) ? atoi(v) : -1;
+    if (mode == 0) return false;
+    if (mode == 1) return true;
+    return num_knots <= (env_max >= 0 ? env_max : max_knots);
 }
 
 // Number of CTAs the global state scratch attached to a robot model serves on the current device: a pure function

@@ -37,45 +37,74 @@
 constexpr int MAX_DEVICES = 16;
 constexpr int N = grid::NUM_JOINTS;
 
-// robot model handle (owns the optional global state scratch) per device and scalar type
+// Robot model handles per device and scalar type.  A handle owns the global scratch that some kernels use for
+// per-thread state / transposed output (cfg::NEEDS_SCRATCH): the scratch is indexed by CTA, so at most ONE such
+// kernel may be in flight per handle.  Launches are stream-ordered, hence one scratch-owning handle per
+// (device, stream), created on the first scratch-using launch on that stream; kernels that never touch the
+// scratch share one scratch-less handle per device.  (Round-1 had one scratch per device: two chunks of the host
+// pipeline, or two user streams, ran Atlas / HyQ gradient kernels concurrently on the same scratch blocks.)
 template <typename T>
 struct Models {
-    grid::robotModel<T>* d_model[MAX_DEVICES] = {};
+    struct Owned { int dev; cudaStream_t stream; grid::robotModel<T>* m; unsigned long last_use; };
+    static constexpr int MAX_OWNED = 32;
+    grid::robotModel<T>* plain[MAX_DEVICES] = {};
+    Owned owned[MAX_OWNED] = {};
+    int nowned = 0;
+    unsigned long tick = 0;
     std::mutex mu;
-    grid::robotModel<T>* get() {
+    grid::robotModel<T>* get(cudaStream_t st, bool needs_scratch) {
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return nullptr;
         std::lock_guard<std::mutex> lk(mu);
-        if (!d_model[dev]) d_model[dev] = grid::init_robotModel<T>();
-        return d_model[dev];
+        if (!needs_scratch) {
+            if (!plain[dev]) plain[dev] = grid::init_robotModel<T>(false);
+            return plain[dev];
+        }
+        ++tick;
+        for (int i = 0; i < nowned; i++)
+            if (owned[i].dev == dev && owned[i].stream == st) { owned[i].last_use = tick; return owned[i].m; }
+        if (nowned < MAX_OWNED) {
+            owned[nowned] = Owned{dev, st, grid::init_robotModel<T>(true), tick};
+            return owned[nowned++].m;
+        }
+        // pool exhausted: hand the least recently used handle of this device to the new stream once its work is done
+        int lru = -1;
+        for (int i = 0; i < nowned; i++)
+            if (owned[i].dev == dev && (lru < 0 || owned[i].last_use < owned[lru].last_use)) lru = i;
+        if (lru < 0) return nullptr;
+        if (cudaStreamSynchronize(owned[lru].stream) != cudaSuccess) { cudaGetLastError(); cudaDeviceSynchronize(); }
+        owned[lru].stream = st; owned[lru].last_use = tick;
+        return owned[lru].m;
     }
     void release() {
         std::lock_guard<std::mutex> lk(mu);
         int cur = 0;
         cudaGetDevice(&cur);
         for (int d = 0; d < MAX_DEVICES; d++)
-            if (d_model[d]) {
+            if (plain[d]) {
                 cudaSetDevice(d);
-                grid::close_grid<T>(nullptr, d_model[d], nullptr);
-                d_model[d] = nullptr;
+                grid::close_grid<T>(nullptr, plain[d], nullptr);
+                plain[d] = nullptr;
             }
+        for (int i = 0; i < nowned; i++) {
+            cudaSetDevice(owned[i].dev);
+            grid::close_grid<T>(nullptr, owned[i].m, nullptr);
+        }
+        nowned = 0;
         cudaSetDevice(cur);
     }
 };
 
-// cached device workspace + streams of the host-buffer entry points (current device only)
+// cached device workspace + streams of the host-buffer entry points, one per device (a host thread driving
+// device d only ever takes device d's lock)
 struct HostWork {
     void* d_in = nullptr; void* d_in2 = nullptr; void* d_out = nullptr;
     size_t in_bytes = 0, in2_bytes = 0, out_bytes = 0;
     cudaStream_t streams[3] = {};
     bool have_streams = false;
-    int device = -1;
     std::mutex mu;
     cudaError_t ensure(size_t in_b, size_t in2_b, size_t out_b) {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (dev != device) { free_all(); device = dev; }
+        cudaError_t e;
         if (!have_streams) {
             for (int i = 0; i < 3; i++)
                 if ((e = cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
@@ -106,12 +135,12 @@ struct HostWork {
 // ---- state shared by all parts of one library (hidden: not visible to other libgrid_<robot>.so files)
 HIDDEN extern Models<float> grid_capi_models_f32;
 HIDDEN extern Models<double> grid_capi_models_f64;
-HIDDEN extern HostWork grid_capi_host_work;
+HIDDEN extern HostWork grid_capi_host_work[MAX_DEVICES];
 HIDDEN std::string& grid_capi_last_error();
 #if HAS(PART_CORE) && (GRID_DTYPES & 1)
 Models<float> grid_capi_models_f32;
 Models<double> grid_capi_models_f64;
-HostWork grid_capi_host_work;
+HostWork grid_capi_host_work[MAX_DEVICES];
 std::string& grid_capi_last_error() { static thread_local std::string s; return s; }
 #endif
 
@@ -130,12 +159,18 @@ int bad_arg(const char* where, const char* what) {
     grid_capi_last_error() = std::string(where) + ": " + what;
     return static_cast<int>(cudaErrorInvalidValue);
 }
-#define GRID_CHECK_ARGS(FN, COND)                                                       \
+#define GRID_CHECK_ARGS(FN, COND, NEEDS_SCRATCH)                                        \
     const char* fn = FN;                                                                \
     if (COND) return bad_arg(fn, "bad pointer / stride / num_knots");                   \
-    auto* m = models<T>().get();                                                        \
-    if (!m) return bad_arg(fn, "no CUDA device");                                       \
-    cudaStream_t st = static_cast<cudaStream_t>(s); (void)st
+    cudaStream_t st = static_cast<cudaStream_t>(s);                                     \
+    auto* m = models<T>().get(st, NEEDS_SCRATCH);                                       \
+    if (!m) return bad_arg(fn, "no CUDA device / robot model")
+
+inline HostWork* host_work() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return nullptr;
+    return &grid_capi_host_work[dev];
+}
 
 // ---- host-buffer entry points.  Two transports, chosen per call:
 //  * pipeline (default for pageable or unmapped buffers): chunks of the batch rotate over three streams so that
@@ -157,7 +192,9 @@ template <typename T, class Launch>
 int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int out_per_knot, int nk, Launch launch) {
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
-    HostWork& w = grid_capi_host_work;
+    HostWork* wp = host_work();
+    if (!wp) return bad_arg(fn, "no CUDA device");
+    HostWork& w = *wp;
     std::lock_guard<std::mutex> lk(w.mu);
     cudaError_t e;
     static const int zero_copy = env_int("GRID_HOST_ZEROCOPY", 0);
@@ -228,18 +265,19 @@ DECL_INFO(core) DECL_INFO(id_du) DECL_INFO(fd_du) DECL_INFO(fd_du_qm) DECL_INFO(
 namespace {
 template <typename T>
 int inverse_dynamics_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_c, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_inverse_dynamics", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_c)));
+    GRID_CHECK_ARGS("grid_inverse_dynamics", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_c)),
+                    grid::inverse_dynamics_cfg<T>::NEEDS_SCRATCH || grid::inverse_dynamics_qdd_cfg<T>::NEEDS_SCRATCH);
     return fail(d_qdd ? grid::inverse_dynamics_qdd_launch<T>(d_c, d_q_qd, stride, d_qdd, m, g, nk, st)
                       : grid::inverse_dynamics_launch<T>(d_c, d_q_qd, stride, m, g, nk, st), fn);
 }
 template <typename T>
 int direct_minv_impl(const T* d_q, int stride, T* d_Minv, int nk, void* s) {
-    GRID_CHECK_ARGS("grid_direct_minv", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_Minv)));
+    GRID_CHECK_ARGS("grid_direct_minv", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_Minv)), grid::direct_minv_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::direct_minv_launch<T>(d_Minv, d_q, stride, m, nk, st), fn);
 }
 template <typename T>
 int forward_dynamics_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_forward_dynamics", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)));
+    GRID_CHECK_ARGS("grid_forward_dynamics", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)), grid::forward_dynamics_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::forward_dynamics_launch<T>(d_qdd, d_in, stride, m, g, nk, st), fn);
 }
 template <typename T>
@@ -303,7 +341,9 @@ int grid_inverse_dynamics_host_f32(const float* h_in, float* h_out, int nk, floa
     const char* fn = "grid_inverse_dynamics_host";
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
-    HostWork& w = grid_capi_host_work;
+    HostWork* wp = host_work();
+    if (!wp) return bad_arg(fn, "no CUDA device");
+    HostWork& w = *wp;
     std::lock_guard<std::mutex> lk(w.mu);
     cudaError_t e = w.ensure(size_t(nk) * 3 * N * sizeof(float), size_t(nk) * N * sizeof(float), size_t(nk) * N * sizeof(float));
     if (e != cudaSuccess) return fail(e, fn);
@@ -320,7 +360,17 @@ int grid_inverse_dynamics_host_f32(const float* h_in, float* h_out, int nk, floa
     return fail(cudaStreamSynchronize(st), fn);
 }
 int grid_release(void) {
-    grid_capi_host_work.free_all();
+    {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (int d = 0; d < MAX_DEVICES; d++)
+            if (grid_capi_host_work[d].have_streams || grid_capi_host_work[d].d_in || grid_capi_host_work[d].d_out) {
+                std::lock_guard<std::mutex> lk(grid_capi_host_work[d].mu);
+                cudaSetDevice(d);
+                grid_capi_host_work[d].free_all();
+            }
+        cudaSetDevice(cur);
+    }
     grid_capi_models_f32.release();
     grid_capi_models_f64.release();
     return 0;
@@ -334,7 +384,8 @@ int grid_release(void) {
 namespace {
 template <typename T>
 int inverse_dynamics_gradient_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_out, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_inverse_dynamics_gradient", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_out)));
+    GRID_CHECK_ARGS("grid_inverse_dynamics_gradient", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_out)),
+                    grid::inverse_dynamics_gradient_cfg<T>::NEEDS_SCRATCH || grid::inverse_dynamics_gradient_qdd_cfg<T>::NEEDS_SCRATCH);
     return fail(d_qdd ? grid::inverse_dynamics_gradient_qdd_launch<T>(d_out, d_q_qd, stride, d_qdd, m, g, nk, st)
                       : grid::inverse_dynamics_gradient_launch<T>(d_out, d_q_qd, stride, m, g, nk, st), fn);
 }
@@ -362,9 +413,10 @@ GRID_FOR_DTYPES(X_ID_DU)
 #if HAS(PART_FD_DU)
 namespace {
 template <typename T>
-int forward_dynamics_gradient_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_forward_dynamics_gradient", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));
-    return fail(grid::forward_dynamics_gradient_launch<T>(d_out, d_in, stride, m, g, nk, st), fn);
+int forward_dynamics_gradient_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s, int form = -1) {
+    GRID_CHECK_ARGS("grid_forward_dynamics_gradient", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)),
+                    grid::forward_dynamics_gradient_cfg<T>::NEEDS_SCRATCH);
+    return fail(grid::forward_dynamics_gradient_launch<T>(d_out, d_in, stride, m, g, nk, st, form), fn);
 }
 template <typename T>
 long info_fd_du(int algo, int what) {
@@ -380,9 +432,11 @@ long info_fd_du(int algo, int what) {
     extern "C" int grid_forward_dynamics_gradient_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {          \
         return forward_dynamics_gradient_impl<T>(a, st, o, nk, g, s); }                                            \
     extern "C" int grid_forward_dynamics_gradient_host_##SUF(const T* h_in, T* h_out, int nk, T g) {               \
+        /* one kernel form for the whole batch, so that the chunked result equals the device entry point's */     \
+        const int form = grid::forward_dynamics_gradient_form_for<T>(nk);                                          \
         return host_pipeline<T>("grid_forward_dynamics_gradient_host", h_in, 3 * N, h_out, 2 * N * N, nk,          \
-            [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
-                return forward_dynamics_gradient_impl<T>(di, 3 * N, dout, c, g, st); }); }
+            [g, form](const T* di, T* dout, int c, cudaStream_t st) {                                              \
+                return forward_dynamics_gradient_impl<T>(di, 3 * N, dout, c, g, st, form); }); }
 GRID_FOR_DTYPES(X_FD_DU)
 #endif
 
@@ -390,9 +444,10 @@ GRID_FOR_DTYPES(X_FD_DU)
 #if HAS(PART_FD_LIN)
 namespace {
 template <typename T>
-int forward_dynamics_linearization_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_forward_dynamics_linearization", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));
-    return fail(grid::forward_dynamics_linearization_launch<T>(d_out, d_in, stride, m, g, nk, st), fn);
+int forward_dynamics_linearization_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s, int form = -1) {
+    GRID_CHECK_ARGS("grid_forward_dynamics_linearization", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)),
+                    grid::forward_dynamics_linearization_cfg<T>::NEEDS_SCRATCH);
+    return fail(grid::forward_dynamics_linearization_launch<T>(d_out, d_in, stride, m, g, nk, st, form), fn);
 }
 template <typename T>
 long info_fd_lin(int algo, int what) {
@@ -408,9 +463,10 @@ long info_fd_lin(int algo, int what) {
     extern "C" int grid_forward_dynamics_linearization_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {     \
         return forward_dynamics_linearization_impl<T>(a, st, o, nk, g, s); }                                       \
     extern "C" int grid_forward_dynamics_linearization_host_##SUF(const T* h_in, T* h_out, int nk, T g) {          \
+        const int form = grid::forward_dynamics_linearization_form_for<T>(nk);                                     \
         return host_pipeline<T>("grid_forward_dynamics_linearization_host", h_in, 3 * N, h_out, 3 * N * N + N, nk, \
-            [g](const T* di, T* dout, int c, cudaStream_t st) {                                                    \
-                return forward_dynamics_linearization_impl<T>(di, 3 * N, dout, c, g, st); }); }
+            [g, form](const T* di, T* dout, int c, cudaStream_t st) {                                              \
+                return forward_dynamics_linearization_impl<T>(di, 3 * N, dout, c, g, st, form); }); }
 GRID_FOR_DTYPES(X_FD_LIN)
 #endif
 
@@ -420,7 +476,8 @@ template <typename T>
 int forward_dynamics_gradient_qdd_minv_impl(const T* d_q_qd, int stride, const T* d_qdd, const T* d_Minv, T* d_out,
                                             int nk, T g, void* s) {
     GRID_CHECK_ARGS("grid_forward_dynamics_gradient_qdd_minv",
-                    nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_qdd || !d_Minv || !d_out)));
+                    nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_qdd || !d_Minv || !d_out)),
+                    grid::forward_dynamics_gradient_qdd_minv_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::forward_dynamics_gradient_qdd_minv_launch<T>(d_out, d_q_qd, stride, d_qdd, d_Minv, m, g, nk, st), fn);
 }
 template <typename T>
@@ -445,12 +502,12 @@ GRID_FOR_DTYPES(X_FD_DU_QM)
 namespace {
 template <typename T>
 int aba_impl(const T* d_in, int stride, T* d_qdd, int nk, T g, void* s) {
-    GRID_CHECK_ARGS("grid_aba", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)));
+    GRID_CHECK_ARGS("grid_aba", nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_qdd)), grid::aba_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::aba_launch<T>(d_qdd, d_in, stride, m, g, nk, st), fn);
 }
 template <typename T>
 int crba_impl(const T* d_q, int stride, T* d_M, int nk, void* s) {
-    GRID_CHECK_ARGS("grid_crba", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_M)));
+    GRID_CHECK_ARGS("grid_crba", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_M)), grid::crba_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::crba_launch<T>(d_M, d_q, stride, m, T(0), nk, st), fn);
 }
 template <typename T>
@@ -475,7 +532,8 @@ GRID_FOR_DTYPES(X_ABA_CRBA)
 #define X_SO(NAME, LAUNCH, CFG, ALGO, KERNEL, IDX)                                                                 \
     namespace {                                                                                                    \
     template <typename T> int NAME##_impl(const T* d_in, int stride, T* d_out, int nk, T g, void* s) {            \
-        GRID_CHECK_ARGS("grid_" #NAME, nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)));                 \
+        GRID_CHECK_ARGS("grid_" #NAME, nk < 0 || stride < 3 * N || (nk > 0 && (!d_in || !d_out)),                  \
+                        grid::CFG<T>::NEEDS_SCRATCH);                                                              \
         return fail(grid::LAUNCH<T>(d_out, d_in, stride, m, g, nk, st), fn);                                       \
     }                                                                                                              \
     template <typename T> long info_##NAME(int algo, int what) {                                                   \
@@ -520,18 +578,20 @@ GRID_FOR_DTYPES(X_FDSVA)
 namespace {
 template <typename T>
 int ee_pose_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
-    GRID_CHECK_ARGS("grid_end_effector_pose", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)));
+    GRID_CHECK_ARGS("grid_end_effector_pose", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)), grid::end_effector_pose_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::end_effector_pose_launch<T>(d_out, d_q, stride, m, nk, st), fn);
 }
 template <typename T>
 int ee_grad_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
-    GRID_CHECK_ARGS("grid_end_effector_pose_gradient", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)));
+    GRID_CHECK_ARGS("grid_end_effector_pose_gradient", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)),
+                    grid::end_effector_pose_gradient_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::end_effector_pose_gradient_launch<T>(d_out, d_q, stride, m, nk, st), fn);
 }
 template <typename T>
 int ee_hess_impl(const T* d_q, int stride, T* d_grad, T* d_hess, int nk, void* s) {
 #if GRID_HAS_EE_HESSIAN
-    GRID_CHECK_ARGS("grid_end_effector_pose_gradient_hessian", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_hess)));
+    GRID_CHECK_ARGS("grid_end_effector_pose_gradient_hessian", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_hess)),
+                    grid::end_effector_pose_gradient_cfg<T>::NEEDS_SCRATCH || grid::end_effector_pose_gradient_hessian_cfg<T>::NEEDS_SCRATCH);
     if (d_grad) {
         cudaError_t e = grid::end_effector_pose_gradient_launch<T>(d_grad, d_q, stride, m, nk, st);
         if (e != cudaSuccess) return fail(e, fn);

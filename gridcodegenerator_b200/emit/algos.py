@@ -355,8 +355,8 @@ def pairs_from_column(n: int) -> int:
     return int(v) if v else n
 
 
-def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
-    """Analytical dc/dq and dc/dqd, one derivative column c at a time.  Needs v, Iv, Xa and the accumulated f in
+def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink, cols: Optional[Sequence[int]] = None):
+    """Analytical dc/dq and dc/dqd, one derivative column c at a time (all columns, or only `cols`).  Needs v, Iv, Xa and the accumulated f in
     the state (rnea_forward(keep=True) + rnea_backward(keep_f=True)).  Follows reference _test.py:229-488; the
     column of joint c touches only subtree(c) (forward) and subtree(c) + ancestors(c) (backward), which is the
     reference's column compression (algorithms/_inverse_dynamics_gradient.py:55-98) made static.
@@ -386,7 +386,7 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink):
             return [(x, y) for x, y in zip(*outs)]
         return run
 
-    for c in range(n):
+    for c in (range(n) if cols is None else cols):
         packed = c >= first_packed
         em.comment(f"grad RNEA column {c}")
         sub = m.subtree[c]
@@ -1316,3 +1316,176 @@ def body_end_effector_pose_gradient_hessian(model: Model) -> Body:
                 for j in range(n):
                     _out(cx.em, (e_ * 6 + o) * n * n + i * n + j, _d2(v, i, j))
     return Body("end_effector_pose_gradient_hessian_inner", "", cx, "Hessian of the end-effector poses")
+
+
+# ============================================================ split (warp-specialised) bodies
+class SplitBody:
+    """One algorithm emitted as  phase A (first-order passes, one warp, publishes the per-knot state in shared memory)
+    +  one function per derivative column (phase B: the columns of a tile run concurrently on the warps of the CTA).
+
+    The per-knot state (v, Iv, X a_parent, f, L, 1/D, sin/cos, qd: 217 values for iiwa14) is what the reference
+    keeps in shared memory between its __syncthreads phases (algorithms/_inverse_dynamics_gradient.py:27-140); here
+    it is written once by phase A as S[slot*32 + lane] and read by the column functions."""
+
+    def __init__(self, name: str, cx: Ctx, doc: str, phase_a: Em, columns):
+        self.name, self.doc = name, doc
+        self.code = phase_a.code()
+        self.nslots = phase_a.nslots
+        self.n_ops = phase_a.n_ops + sum(e.n_ops for _, e in columns)
+        self.phase_a_ops = phase_a.n_ops
+        self.columns = [(c, e.code(), e.n_ops) for c, e in columns]
+
+
+def _publish_state(cx: Ctx, qd: Sequence[V], extra=()):
+    """End of phase A: make every value the column functions read a shared state slot.  Small robots run phase A
+    on SSA values (registers), so the values are stored now; big robots already keep them in slots."""
+    em, m, n = cx.em, cx.m, cx.n
+    em.comment("---- publish the per-knot state for the column functions")
+    keys = []
+    for j in range(n):
+        for nm in ("v", "Iv", "Xa", "f"):
+            keys += [(nm, j, k) for k in range(6)]
+    keys += list(extra)
+    pending = []
+    if em.regs_only:
+        for key in keys:
+            if key in em.const_slots:
+                continue
+            pending.append((key, em.reg_state[key]))
+        em.regs_only = False
+    for key, v in pending:
+        em.store(key, v)
+    for j in range(n):
+        sn, cs, qv = cx.trig[j]
+        if sn is not None:
+            em.store(("sn", j, 0), V(s=sn.s))
+            em.store(("cs", j, 0), V(s=cs.s))
+        else:
+            em.store(("qv", j, 0), V(s=qv.s))
+        em.store(("qd", j, 0), V(s=qd[j].s))
+
+
+def _column_ctx(cx: Ctx, c: int) -> Ctx:
+    """Context of the function of derivative column c: reloads sin/cos and qd of the joints the column touches."""
+    m = cx.m
+    emc = cx.em.fork()
+    cc = Ctx.__new__(Ctx)
+    cc.m, cc.em, cc.n, cc.gravity = m, emc, cx.n, cx.gravity
+    touched = sorted(set(m.subtree[c]) | set(m.ancestors[c]))
+    cc.X = [None] * m.n
+    cc.trig = [None] * m.n
+    cc.q = [None] * m.n
+    qd: List[Optional[V]] = [None] * m.n
+    for j in touched:
+        jd = m.joints[j]
+        if jd.revolute:
+            sn = emc.named(f"sn{j}", emc.load(("sn", j, 0)).s)
+            cs = emc.named(f"cs{j}", emc.load(("cs", j, 0)).s)
+            tr = Trig(sn, cs, None)
+        else:
+            tr = Trig(None, None, emc.named(f"q_{j}", emc.load(("qv", j, 0)).s))
+        cc.X[j] = Xform(jd, tr)
+        if j in m.subtree[c]:
+            qd[j] = emc.named(f"qd_{j}", emc.load(("qd", j, 0)).s)
+    cc.qd = qd
+    return cc
+
+
+def split_enabled(n: int) -> bool:
+    """Split bodies are emitted for grad ID / grad FD / the FD linearisation of every robot unless GRID_SPLIT=0."""
+    return os.environ.get("GRID_SPLIT", "1") != "0"
+
+
+def split_phase_a_regs_policy(n: int) -> bool:
+    """Phase A on SSA values (registers) for small robots, on state slots otherwise."""
+    mode = os.environ.get("GRID_SPLIT_PHASEA_REGS", "auto")
+    if mode in ("0", "1"):
+        return mode == "1"
+    return regs_only_policy(n)
+
+
+def _split_columns(cx: Ctx, sink_factory):
+    cols = []
+    for c in range(cx.n):
+        cc = _column_ctx(cx, c)
+        rnea_grad_columns(cc, cc.qd, sink_factory(cc), cols=[c])
+        cols.append((c, cc.em))
+    return cols
+
+
+def split_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> SplitBody:
+    cx = Ctx(model)
+    em, n = cx.em, model.n
+    em.no_sync = True
+    em.regs_only = split_phase_a_regs_policy(n)
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_") if use_qdd else None
+    rnea_forward(cx, qd, qdd, keep=True)
+    rnea_backward(cx, qd, keep_f=True)
+    _publish_state(cx, qd)
+
+    def sink_factory(cc):
+        def sink(c, dc):
+            for r in range(n):
+                x, y = _halves(cc.em, dc[r])
+                _out(cc.em, c * n + r, x)
+                _out(cc.em, (n + c) * n + r, y)
+        return sink
+
+    cols = _split_columns(cx, sink_factory)
+    return SplitBody("inverse_dynamics_gradient", cx, "[dc/dq | dc/dqd], column-major n x 2n", em, cols)
+
+
+def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -> SplitBody:
+    """grad FD (optionally with the Minv and qdd side outputs) in split form: phase A = RNEA(q, qd, 0), CRBA,
+    L^T D L, qdd, RNEA(q, qd, qdd); phase B = one function per column c computing dc/dq_c, dc/dqd_c and the two
+    solves -M^-1 dc against the published factors."""
+    cx = Ctx(model)
+    em, n = cx.em, model.n
+    em.no_sync = True
+    em.regs_only = split_phase_a_regs_policy(n)
+    cx.prologue()
+    qd = cx.read_vec("qd", "qd_")
+    u = cx.read_vec("u", "u_")
+    em.comment("---- phase A, pass 1: bias forces c = RNEA(q, qd, 0)")
+    rnea_forward(cx, qd, None, keep=False)
+    c = rnea_backward(cx, qd, keep_f=False)
+    em.comment("---- M = CRBA(q), M = L^T D L")
+    Mv = crba_matrix(cx)
+    L, Dinv = ltdl_factor(cx, Mv)
+    for k_, v_ in L.items():
+        em.store(("L",) + k_, v_)
+    for i_, v_ in enumerate(Dinv):
+        em.store(("Dinv2", i_, 0), v_)
+    qdd = ltdl_solve(cx, L, Dinv, [em.sub(u[j], c[j]) for j in range(n)])
+    if linearization:
+        em.comment("---- side outputs: Minv (dense symmetric, column-major) and qdd")
+        cols_ = [ltdl_solve(cx, L, Dinv, [ONE if r == k else ZERO for r in range(n)]) for k in range(n)]
+        for k in range(n):
+            for r in range(n):
+                _out(em, (2 * n + k) * n + r, cols_[k][r] if r <= k else cols_[r][k])
+        for j in range(n):
+            _out(em, 3 * n * n + j, qdd[j])
+    em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
+    rnea_forward(cx, qd, qdd, keep=True)
+    rnea_backward(cx, qd, keep_f=True)
+    lkeys = [("L",) + k_ for k_ in L] + [("Dinv2", i_, 0) for i_ in range(n)]
+    _publish_state(cx, qd, extra=lkeys)
+
+    def sink_factory(cc):
+        def sink(c_, dc):
+            e = cc.em
+            Ll = {k_: e.load(("L",) + k_) for k_ in L}
+            Dl = [e.load(("Dinv2", i_, 0)) for i_ in range(n)]
+            for h in (0, 1):
+                x = ltdl_solve(cc, Ll, Dl, [_halves(e, d_)[h] for d_ in dc], sign=-1.0)
+                for r in range(n):
+                    _out(e, (h * n + c_) * n + r, x[r])
+        return sink
+
+    cols = _split_columns(cx, sink_factory)
+    if linearization:
+        return SplitBody("forward_dynamics_linearization", cx,
+                         "[dqdd/dq | dqdd/dqd | Minv | qdd]: grad FD with its Minv and qdd by-products", em, cols)
+    return SplitBody("forward_dynamics_gradient", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]", em, cols)

@@ -79,6 +79,9 @@ class Em:
         self.reg_state: Dict[Tuple, V] = {}
         # emit-time forward-mode AD: 0 = off, 1 = first-order tangents, 2 = also second order
         self._nsync = 0
+        self.no_sync = False        # split (warp-specialised) bodies: warps run different code, no lockstep barriers
+        self.private_regs = False   # column functions of the split mode: column-private values (tuple-named keys) are SSA
+        self.frozen = False         # ... and the shared state is read-only
         self.ad_order = 0
         self._ad_depth = 0
         self._ad_cap = None
@@ -97,7 +100,7 @@ class Em:
         # lockstep point: the warps of a CTA re-converge here so that they stream the (straight-line, >100 KB)
         # code through the instruction caches together; a no-op for single-warp CTAs
         self._nsync += 1
-        if SYNC_EVERY > 0 and self._nsync % SYNC_EVERY == 0:
+        if SYNC_EVERY > 0 and self._nsync % SYNC_EVERY == 0 and not self.no_sync:
             self.lines.append("GRID_SYNC();")
 
     def tmp(self, expr: str) -> V:
@@ -131,6 +134,16 @@ class Em:
     def named(self, name: str, expr: str) -> V:
         self.lines.append(f"const T {name} = {expr};")
         return V(s=name)
+
+    def fork(self) -> "Em":
+        """Emitter for a function that runs AFTER this one on the same per-knot state (split mode: the derivative
+        columns, each on its own warp): same slot map and emit-time constants, read-only; values stored under
+        column-private keys (tuple-valued names such as ("df", c)) stay SSA values of the new function."""
+        e = Em(self.state_name, self.stride_name)
+        e.slots, e.const_slots, e.nslots = self.slots, self.const_slots, self.nslots
+        e.fences, e.no_sync = self.fences, True
+        e.regs_only, e.private_regs, e.frozen = False, True, True
+        return e
 
     def code(self, indent: str = "    ") -> str:
         return "\n".join(indent + l for l in self.lines) + "\n"
@@ -447,6 +460,11 @@ class Em:
 
     def release(self, *key):
         """Return a slot to the pool (its value is dead from here on)."""
+        if self.private_regs and isinstance(key[0], tuple):
+            self.reg_state.pop(key, None)
+            return
+        if self.frozen:
+            return
         for k in (key, key + ("x",), key + ("y",)):
             idx = self.slots.pop(k, None)
             if idx is not None:
@@ -454,10 +472,17 @@ class Em:
 
     def store(self, key: Tuple, v: V):
         """Store v into the state slot `key`; constants are remembered at emit time, not stored."""
+        if self.private_regs and isinstance(key[0], tuple):
+            self.reg_state[key] = v
+            return
         if v.is_const:
+            if self.frozen:
+                raise ValueError(f"store to shared state {key} from a read-only (column) emitter")
             self.const_slots[key] = v.c
             self.release(*key)
             return
+        if self.frozen:
+            raise ValueError(f"store to shared state {key} from a read-only (column) emitter")
         self.const_slots.pop(key, None)
         if self.regs_only:
             self.reg_state[key] = v
@@ -478,6 +503,8 @@ class Em:
         self.lines.append(f"{self.state_name}[{idx}*{self.stride_name}] = {v.s};")
 
     def load(self, key: Tuple) -> V:
+        if self.private_regs and key in self.reg_state:
+            return self.reg_state[key]
         if key in self.const_slots:
             return const(self.const_slots[key])
         if self.regs_only:

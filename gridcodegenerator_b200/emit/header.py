@@ -180,7 +180,130 @@ def emit_config(sp: AlgoSpec, body: algos.Body, n: int) -> str:
             f"    static constexpr bool STATE_SMEM = sizeof(T) == 4 ? {b(c4[1])} : {b(c8[1])};\n"
             f"    static constexpr int STAGED = sizeof(T) == 4 ? {int(c4[2])} : {int(c8[2])};\n"
             f"    static constexpr size_t SMEM_BYTES = grid_rt::tile_smem_bytes<{A}<T>, T, NT, STATE_SMEM, STAGED>();\n"
+            f"    // the kernel uses d_robotModel->d_scratch: at most ONE such launch may be in flight per robotModel\n"
+            f"    static constexpr bool NEEDS_SCRATCH = !STATE_SMEM || STAGED == 3;\n"
             f"}};\n\n")
+
+
+# ------------------------------------------------------------------ split (warp-specialised) form
+SPLIT_KEYS = {"inverse_dynamics_gradient": lambda m, tag: algos.split_inverse_dynamics_gradient(m, tag == "_qdd"),
+              "forward_dynamics_gradient": lambda m, tag: algos.split_forward_dynamics_gradient(m, False),
+              "forward_dynamics_linearization": lambda m, tag: algos.split_forward_dynamics_gradient(m, True)}
+SPLIT_MAX_WARPS = int(os.environ.get("GRID_SPLIT_MAX_WARPS", "16"))
+
+
+def has_split(sp: AlgoSpec, n: int) -> bool:
+    return algos.split_enabled(n) and sp.key in SPLIT_KEYS and sp.tag in ("", "_qdd")
+
+
+def split_body(sp: AlgoSpec, model: Model) -> "algos.SplitBody":
+    return SPLIT_KEYS[sp.key](model, sp.tag)
+
+
+def split_assign(sb: "algos.SplitBody", max_warps: int = 0):
+    """Columns -> warps, longest-processing-time first.  The number of warps is the smallest that brings the
+    heaviest warp within 5 % of the heaviest single column (more warps cannot shorten phase B), at most
+    SPLIT_MAX_WARPS.  Returns a list (one entry per warp) of column lists."""
+    max_warps = max_warps or SPLIT_MAX_WARPS
+    cols = sorted(((ops, c) for c, _, ops in sb.columns), reverse=True)
+    forced = os.environ.get("GRID_SPLIT_WARPS", "")
+    best = None
+    for nw in ([int(forced)] if forced else range(1, max_warps + 1)):
+        load = [0] * nw
+        groups = [[] for _ in range(nw)]
+        for ops, c in cols:
+            w = load.index(min(load))
+            load[w] += ops
+            groups[w].append(c)
+        best = groups
+        if max(load) <= 1.05 * cols[0][0]:
+            break
+    return [sorted(g) for g in best if g]
+
+
+def split_out_staged(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> bool:
+    a16 = lambda x: (x + 15) & ~15
+    need = a16(max(sb.nslots, 1) * 32 * sizeof) + sum(2 * a16(32 * e * sizeof) for _, e in sp.streams) \
+        + a16(32 * sp.out_n(n) * sizeof) + 32
+    return need <= SMEM_LIMIT
+
+
+def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1) -> str:
+    """phase A + column functions + algo struct + config + kernel of the split form of one algorithm."""
+    stem = f"{sp.fn}{sp.tag}_split"
+    ins = "".join(f"const T* __restrict__ {p}, " for p in sp.inner_inputs)
+    grav = "const T gravity" if sp.uses_gravity else "const T /*gravity*/"
+    pre = "    using grid_rt::grid_sincos;\n    typedef grid_rt::pair_t<T> P;\n"
+    out = [f"/**\n * {sb.doc} -- SPLIT form, phase A: the first-order passes of one knot per lane; publishes the per-knot\n"
+           f" * state as S[slot*NT] ({sb.nslots} slots).  Emitted operations (mul+add): {sb.phase_a_ops}\n */\n"
+           f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
+           f"void {stem}_phaseA(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n" + pre + sb.code + "}\n\n"]
+    for c, code, ops in sb.columns:
+        out.append(f"/** SPLIT form, derivative column {c} (dq_{c} and dqd_{c}) of {sp.fn}: reads the published state, "
+                   f"writes its output entries.  Emitted operations: {ops} */\n"
+                   f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
+                   f"void {stem}_col{c}(T* __restrict__ o, T* __restrict__ S) {{\n" + pre + code + "}\n\n")
+    groups = split_assign(sb)
+    nw = len(groups)
+    IN = [e for _, e in sp.streams] + [0, 0, 0]
+    args = []
+    for (s_, off) in sp.split:
+        args.append(f"x{s_}" + (f" + {off}" if off else ""))
+    cases = []
+    for w, g in enumerate(groups):
+        calls = " ".join(f"{stem}_col{c}<T, NT, OS>(o, S);" for c in g)
+        cases.append(f"            case {w}: {calls} break;")
+    writes = "GRID_BEFORE_FIRST_OUTPUT" in sb.code
+    out.append(f"template <typename T>\nstruct {stem}_algo {{\n"
+               f"    static constexpr int IN0 = {IN[0]}, IN1 = {IN[1]}, IN2 = {IN[2]};\n"
+               f"    static constexpr int OUT = {sp.out_n(n)};\n"
+               f"    static constexpr int SLOTS = {max(sb.nslots, 1)};\n"
+               f"    static constexpr int NW = {nw};          // warps per CTA = column groups of phase B\n"
+               f"    static constexpr int NA = 1;           // warps running phase A\n"
+               f"    static constexpr bool PHASE_A_WRITES = {'true' if writes else 'false'};\n"
+               f"    template <int NT, int OS>\n"
+               f"    static __device__ __forceinline__ void phaseA(int /*warp*/, T* __restrict__ o, const T* __restrict__ x0, "
+               f"const T* __restrict__ x1, const T* __restrict__ x2, T* __restrict__ S, const T gravity) {{\n"
+               f"        {stem}_phaseA<T, NT, OS>(o, {', '.join(args)}, S, gravity);\n    }}\n"
+               f"    template <int NT, int OS>\n"
+               f"    static __device__ __forceinline__ void phaseB(int warp, T* __restrict__ o, T* __restrict__ S) {{\n"
+               f"        switch (warp) {{\n" + "\n".join(cases) + "\n            default: break;\n        }\n    }\n};\n\n")
+    st4 = split_out_staged(sb, sp, n, 4)
+    st8 = split_out_staged(sb, sp, n, 8)
+    b = lambda x: "true" if x else "false"
+    A = f"{stem}_algo"
+    regs = int(os.environ.get("GRID_SPLIT_MAXNREG", "0"))
+    out.append(f"template <typename T>\nstruct {stem}_cfg {{\n"
+               f"    static constexpr int NT = {nw * 32};\n"
+               f"    static constexpr bool OUT_STAGED = sizeof(T) == 4 ? {b(st4)} : {b(st8)};\n"
+               f"    static constexpr size_t SMEM_BYTES = grid_rt::split_smem_bytes<{A}<T>, T, OUT_STAGED>();\n"
+               f"    static constexpr bool NEEDS_SCRATCH = false;\n"
+               f"    static constexpr bool FITS = SMEM_BYTES <= {SMEM_LIMIT};   // else the split kernel is never launched\n"
+               f"}};\n\n")
+    fill = []
+    for i, (name, e) in enumerate(sp.streams):
+        stride = f"stride_{sp.streams[0][0][2:]}" if i == 0 else str(e)
+        fill.append(f"    a.in[{i}] = {name}; a.stride[{i}] = {stride};")
+    for i in range(len(sp.streams), 3):
+        fill.append(f"    a.in[{i}] = nullptr; a.stride[{i}] = 0;")
+    gv = "gravity" if sp.uses_gravity else "T(0)"
+    C = f"{stem}_cfg<T>"
+    bounds = (f"__maxnreg__({regs})" if regs else f"__maxnreg__(({C}::NT * 255 <= 65536) ? 255 : (65536 / {C}::NT / 8 * 8))")
+    out.append(f"template <typename T>\n__global__ void {bounds}\n"
+               f"{sp.fn}_split_kernel({kernel_params(sp)}) {{\n"
+               f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"
+               f"    grid_rt::TileArgs<T> a;\n" + "\n".join(fill) + "\n"
+               f"    a.out = {sp.out_name}; a.scratch = nullptr;\n"
+               f"    a.gravity = {gv}; a.num_knots = NUM_TIMESTEPS;\n"
+               f"    if ({C}::FITS) grid_rt::tile_loop_split<{A}<T>, T, {C}::OUT_STAGED>(a, grid_smem);\n}}\n\n")
+    # default batch size up to which the launcher prefers the split form (tools/tune_split.py measures the crossover)
+    mono = choose_config(max(mono_slots, 1), [e for _, e in sp.streams], sp.out_n(n), 4)
+    max_knots = (1 << 30) if not mono[1] else SPLIT_DEFAULT_MAX_KNOTS
+    out.append(f"inline int {stem}_max_knots() {{ return {max_knots}; }}\n\n")
+    return "".join(out)
+
+
+SPLIT_DEFAULT_MAX_KNOTS = 2 * 148 * 32
 
 
 def kernel_params(sp: AlgoSpec) -> str:
@@ -255,8 +378,27 @@ def emit_launch(sp: AlgoSpec, n: int) -> str:
     call.append("num_timesteps")
     ps.append("cudaStream_t stream")
     kfn = f"{sp.fn}_kernel<T>"
-    return (f"template <typename T>\n__host__\ncudaError_t {sp.fn}{sp.tag}_launch({', '.join(ps)}) {{\n"
-            f"    if (num_timesteps <= 0) return cudaSuccess;\n"
+    split = form_fn = ""
+    if has_split(sp, n):
+        # `form`: -1 = pick by batch size (<algo>_form_for), 0 = one lane per knot, 1 = split.  The host-buffer entry
+        # points decide once for the whole batch and pass the decision to every chunk's launch.
+        ps.append("int form = -1")
+        SC = f"{sp.fn}{sp.tag}_split_cfg<T>"
+        form_fn = (f"/** Kernel form the launcher uses for a batch of num_timesteps knot points: 1 = split (phase A + columns\n"
+                   f" *  spread over the CTA's warps), 0 = one lane per knot point. */\n"
+                   f"template <typename T>\n__host__\nint {sp.fn}{sp.tag}_form_for(const int num_timesteps) {{\n"
+                   f"    return ({SC}::FITS && grid_rt::use_split_kernel(num_timesteps, {sp.fn}{sp.tag}_split_max_knots())) ? 1 : 0;\n}}\n\n")
+        split = (f"    if (form < 0) form = {sp.fn}{sp.tag}_form_for<T>(num_timesteps);\n"
+                 f"    if (form == 1 && {SC}::FITS) {{\n"
+                 f"        auto skern = static_cast<void (*)({_sig_types(sp)})>({sp.fn}_split_kernel<T>);\n"
+                 f"        int sblocks = grid_rt::persistent_blocks(reinterpret_cast<const void*>(skern), {SC}::NT, "
+                 f"{SC}::SMEM_BYTES, num_timesteps);\n"
+                 f"        if (sblocks <= 0) {{ cudaError_t e = cudaGetLastError(); return e != cudaSuccess ? e : cudaErrorLaunchOutOfResources; }}\n"
+                 f"        cudaError_t se = grid_rt::launch_tile_kernel(skern, sblocks, {SC}::NT, {SC}::SMEM_BYTES, stream, {', '.join(call)});\n"
+                 f"        return se != cudaSuccess ? se : cudaGetLastError();\n"
+                 f"    }}\n")
+    return (form_fn + f"template <typename T>\n__host__\ncudaError_t {sp.fn}{sp.tag}_launch({', '.join(ps)}) {{\n"
+            f"    if (num_timesteps <= 0) return cudaSuccess;\n" + split +
             f"    auto kern = static_cast<void (*)({_sig_types(sp)})>({kfn});\n"
             f"    int blocks = grid_rt::persistent_blocks(reinterpret_cast<const void*>(kern), {C}::NT, "
             f"{C}::SMEM_BYTES, num_timesteps);\n"

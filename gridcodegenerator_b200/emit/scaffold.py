@@ -96,16 +96,18 @@ struct gridData {
 
 LIFECYCLE = """/**
  * Allocates the (device-resident) robot model handle.  The constants of the robot live in the code;
- * the handle owns the optional global state scratch.
+ * the handle owns the optional global state scratch (indexed by CTA: at most ONE scratch-using kernel --
+ * <algo>_cfg<T>::NEEDS_SCRATCH -- may be in flight per handle; use one handle per stream for concurrent launches).
+ * with_scratch = false gives a handle for kernels that never touch the scratch.
  */
 template <typename T>
 __host__
-robotModel<T>* init_robotModel() {
+robotModel<T>* init_robotModel(bool with_scratch = true) {
     robotModel<T> h_model;
     h_model.d_scratch = nullptr; h_model.scratch_blocks = 0;
     h_model.d_XImats = nullptr; h_model.d_topology_helpers = nullptr;
     const size_t per_block = sizeof(T) == 4 ? GRID_SCRATCH_ELEMS_PER_BLOCK_F32 : GRID_SCRATCH_ELEMS_PER_BLOCK_F64;
-    if (per_block > 0) {
+    if (per_block > 0 && with_scratch) {
         h_model.scratch_blocks = grid_rt::scratch_capacity(GRID_SCRATCH_BLOCKS_PER_SM);
         if (h_model.scratch_blocks <= 0) gpuErrchk(cudaErrorInvalidDevice);
         gpuErrchk(cudaMalloc((void**)&h_model.d_scratch, per_block*h_model.scratch_blocks*sizeof(T)));

@@ -51,6 +51,24 @@ def _source_digest(header_text: str) -> str:
     return h.hexdigest()[:16]
 
 
+def _package_digest() -> str:
+    """Digest of everything a library is generated from EXCEPT the robot description: emitter, robot layer, CUDA
+    runtime, C ABI, compile flags.  Cheap (no emission), so GRiDLibrary checks it at load time and refuses a stale
+    binary; build_library() additionally keys on the emitted header itself."""
+    h = hashlib.sha256()
+    files = []
+    for sub in ("emit", "robot", "csrc"):
+        for dp, _, fns in os.walk(os.path.join(_PKG, sub)):
+            files += [os.path.join(dp, f) for f in fns if f.endswith((".py", ".cu", ".cuh", ".urdf"))]
+    files += [os.path.join(_PKG, "GRiDCodeGenerator.py"), os.path.join(INCLUDE, "grid_b200.h")]
+    for fn in sorted(files):
+        h.update(os.path.relpath(fn, _ROOT).encode())
+        with open(fn, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()[:16]
+
+
 def library_path(robot_name: str) -> str:
     return os.path.join(BUILD_DIR, robot_name, f"libgrid_{robot_name}.so")
 
@@ -97,6 +115,8 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
     so = library_path(name)
     stamp = os.path.join(out_dir, "digest.txt")
     if not force and os.path.exists(so) and os.path.exists(stamp) and open(stamp).read().strip() == digest:
+        with open(os.path.join(out_dir, "package_digest.txt"), "w") as f:     # same header => binary still current
+            f.write(_package_digest())
         return so
     own = pool is None
     if own:
@@ -115,7 +135,40 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
         os.remove(o)
     with open(stamp, "w") as f:
         f.write(digest)
+    with open(os.path.join(out_dir, "package_digest.txt"), "w") as f:
+        f.write(_package_digest())
     return so
+
+
+def host_tier_check_path(robot_name: str) -> str:
+    return os.path.join(BUILD_DIR, robot_name, "host_tier_check")
+
+
+def build_host_tier_check(robot, knots: int = 1000, force: bool = False) -> str:
+    """Compile csrc/host_tier_check.cu -- a user program against the emitted grid.cuh's host tier -- for `robot`
+    (build_library must have emitted the header).  tests/test_gpu_host_tier.py runs it and compares its results
+    with the C ABI.  Same code-generation flags as the library, so the kernels are the same machine code."""
+    name = robot if isinstance(robot, str) else robot.name
+    out_dir = os.path.join(BUILD_DIR, name)
+    exe = host_tier_check_path(name)
+    src = os.path.join(CSRC, "host_tier_check.cu")
+    hdr = os.path.join(out_dir, "grid.cuh")
+    h = hashlib.sha256()
+    for fn in (src, hdr):
+        with open(fn, "rb") as f:
+            h.update(f.read())
+    h.update(f"{knots} {' '.join(NVCC_FLAGS)}".encode())
+    stamp = os.path.join(out_dir, "host_tier_digest.txt")
+    if not force and os.path.exists(exe) and os.path.exists(stamp) and open(stamp).read().strip() == h.hexdigest():
+        return exe
+    cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f not in ("-shared", "-Xcompiler", "-fPIC")] + [
+        f"-I{out_dir}", f"-DHOST_TIER_KNOTS={knots}", src, "-o", exe]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for host_tier_check ({name}):\n{res.stdout[-4000:]}")
+    with open(stamp, "w") as f:
+        f.write(h.hexdigest())
+    return exe
 
 
 _f32p = ctypes.c_void_p
@@ -131,6 +184,14 @@ class GRiDLibrary:
             if not build:
                 raise RuntimeError(f"{so} is missing and build=False: no fallback path exists")
             so = build_library(robot)
+        # a binary built from other sources than the ones in the tree must not be used silently
+        stamp = os.path.join(os.path.dirname(so), "package_digest.txt")
+        if os.environ.get("GRID_SKIP_DIGEST_CHECK") != "1":
+            have = open(stamp).read().strip() if os.path.exists(stamp) else None
+            if have != _package_digest():
+                if not build:
+                    raise RuntimeError(f"{so} is stale (built from different emitter / runtime sources) and build=False")
+                so = build_library(robot)
         self.path = so
         self.lib = ctypes.CDLL(so)
         L = self.lib
@@ -187,6 +248,18 @@ class GRiDLibrary:
         return t.data_ptr(), int(t.stride(0)), int(t.shape[0])
 
     @staticmethod
+    def _out(out, like, B: int, m: int):
+        """Allocate the (B, m) result, or validate a caller-supplied one: the kernels write B*m contiguous elements."""
+        import torch
+        if out is None:
+            return torch.empty((B, m), dtype=like.dtype, device=like.device)
+        if not out.is_cuda or out.device != like.device or out.dtype != like.dtype:
+            raise ValueError(f"out must be a {like.dtype} tensor on {like.device}")
+        if tuple(out.shape) != (B, m) or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous ({B}, {m}) tensor, got {tuple(out.shape)} strides {out.stride()}")
+        return out
+
+    @staticmethod
     def _stream():
         import torch
         return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -205,7 +278,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd, 2 * n)
         suf = self._suf(q_qd)
-        out = torch.empty((B, n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        out = self._out(out, q_qd, B, n)
         pq = None
         if qdd is not None:
             pq, sq, Bq = self._dev(qdd, n)
@@ -220,7 +293,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q, n)
         suf = self._suf(q)
-        out = torch.empty((B, n * n), dtype=q.dtype, device=q.device) if out is None else out
+        out = self._out(out, q, B, n * n)
         with torch.cuda.device(q.device):
             self._check(getattr(self.lib, f"grid_direct_minv_{suf}")(p, stride, out.data_ptr(), B, self._stream()))
         return out
@@ -230,7 +303,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd_u, 3 * n)
         suf = self._suf(q_qd_u)
-        out = torch.empty((B, n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        out = self._out(out, q_qd_u, B, n)
         with torch.cuda.device(q_qd_u.device):
             self._check(getattr(self.lib, f"grid_forward_dynamics_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
@@ -240,7 +313,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd, 2 * n)
         suf = self._suf(q_qd)
-        out = torch.empty((B, 2 * n * n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        out = self._out(out, q_qd, B, 2 * n * n)
         pq = None
         if qdd is not None:
             pq, sq, Bq = self._dev(qdd, n)
@@ -255,7 +328,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd_u, 3 * n)
         suf = self._suf(q_qd_u)
-        out = torch.empty((B, 2 * n * n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        out = self._out(out, q_qd_u, B, 2 * n * n)
         with torch.cuda.device(q_qd_u.device):
             self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
@@ -267,7 +340,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd_u, 3 * n)
         suf = self._suf(q_qd_u)
-        out = torch.empty((B, 3 * n * n + n), dtype=q_qd_u.dtype, device=q_qd_u.device) if out is None else out
+        out = self._out(out, q_qd_u, B, 3 * n * n + n)
         with torch.cuda.device(q_qd_u.device):
             self._check(getattr(self.lib, f"grid_forward_dynamics_linearization_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         if split:
@@ -283,7 +356,7 @@ class GRiDLibrary:
         pm, sm, _ = self._dev(Minv, n * n)
         if sq != n or sm != n * n:
             raise ValueError("qdd and Minv must be dense")
-        out = torch.empty((B, 2 * n * n), dtype=q_qd.dtype, device=q_qd.device) if out is None else out
+        out = self._out(out, q_qd, B, 2 * n * n)
         with torch.cuda.device(q_qd.device):
             self._check(getattr(self.lib, f"grid_forward_dynamics_gradient_qdd_minv_{suf}")(
                 p, stride, pq, pm, out.data_ptr(), B, gravity, self._stream()))
@@ -294,7 +367,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q_qd_tau, 3 * n)
         suf = self._suf(q_qd_tau)
-        out = torch.empty((B, n), dtype=q_qd_tau.dtype, device=q_qd_tau.device) if out is None else out
+        out = self._out(out, q_qd_tau, B, n)
         with torch.cuda.device(q_qd_tau.device):
             self._check(getattr(self.lib, f"grid_aba_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
@@ -304,7 +377,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(x, 3 * n)
         suf = self._suf(x)
-        out = torch.empty((B, 4 * n ** 3), dtype=x.dtype, device=x.device) if out is None else out
+        out = self._out(out, x, B, 4 * n ** 3)
         with torch.cuda.device(x.device):
             self._check(getattr(self.lib, f"grid_{fn}_{suf}")(p, stride, out.data_ptr(), B, gravity, self._stream()))
         return out
@@ -321,7 +394,7 @@ class GRiDLibrary:
         """(B, >=n) rows starting with q -> (B, 6*num_ees) [x y z roll pitch yaw] per end effector."""
         import torch
         p, stride, B = self._dev(q, self.n)
-        out = torch.empty((B, 6 * self.num_ees), dtype=q.dtype, device=q.device) if out is None else out
+        out = self._out(out, q, B, 6 * self.num_ees)
         with torch.cuda.device(q.device):
             self._check(getattr(self.lib, f"grid_end_effector_pose_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
         return out
@@ -330,7 +403,7 @@ class GRiDLibrary:
         """-> (B, 6*num_ees*n), index (ee*n + j)*6 + o."""
         import torch
         p, stride, B = self._dev(q, self.n)
-        out = torch.empty((B, 6 * self.num_ees * self.n), dtype=q.dtype, device=q.device) if out is None else out
+        out = self._out(out, q, B, 6 * self.num_ees * self.n)
         with torch.cuda.device(q.device):
             self._check(getattr(self.lib, f"grid_end_effector_pose_gradient_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
         return out
@@ -352,7 +425,7 @@ class GRiDLibrary:
         n = self.n
         p, stride, B = self._dev(q, n)
         suf = self._suf(q)
-        out = torch.empty((B, n * n), dtype=q.dtype, device=q.device) if out is None else out
+        out = self._out(out, q, B, n * n)
         with torch.cuda.device(q.device):
             self._check(getattr(self.lib, f"grid_crba_{suf}")(p, stride, out.data_ptr(), B, self._stream()))
         return out

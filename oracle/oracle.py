@@ -47,6 +47,30 @@ def _arr(x):
     return np.ascontiguousarray(x, dtype=np.float64)
 
 
+def _hom_tables(robot):
+    """Xhom_j(q) = H0 + sin(q) Hs + cos(q) Hc + q Hq per joint (4x4), by evaluating the robot's sympy homogeneous
+    transforms at three angles (revolute) / two displacements (prismatic).  Pinned by tests/test_oracle_golden.py
+    against the sympy-differentiated end-effector fixtures of tools/make_golden.py."""
+    out = []
+    for j, M in enumerate(robot.get_Xmats_hom_ordered_by_id()):
+        syms = list(M.free_symbols)
+        ev = lambda val: np.array(M.subs({s_: val for s_ in syms}).evalf(30), dtype=np.float64).reshape(4, 4)
+        Z = np.zeros((4, 4))
+        if int(np.argmax(np.abs(robot.get_S_by_id(j)))) < 3:
+            A, B, C = ev(0), ev(np.pi / 2), ev(np.pi)
+            H0, Hc = (A + C) / 2, (A - C) / 2
+            Hs = B - H0
+            for m in (H0, Hs, Hc):
+                m[np.abs(m) < 1e-12] = 0.0
+            out.append((H0, Hs, Hc, Z))
+        else:
+            A, B = ev(0), ev(1)
+            D = B - A
+            D[np.abs(D) < 1e-12] = 0.0
+            out.append((A, Z, Z, D))
+    return out
+
+
 class Oracle:
     def __init__(self, robot):
         L = _lib()
@@ -61,9 +85,9 @@ class Oracle:
         if not self._h:
             raise RuntimeError("rbd_model_create failed (n too large?)")
         self.L = L
-        # homogeneous transforms + leaves for the end-effector functions
-        from gridcodegenerator_b200.emit.spatial import hom_tables
-        H = hom_tables(robot)
+        # homogeneous transforms + leaves for the end-effector functions: sampled here from the robot's sympy
+        # matrices (the reference's input, helpers/_topology_helpers.py:76-78), NOT taken from the product's emitter
+        H = _hom_tables(robot)
         hs = [np.ascontiguousarray(np.stack([h[i] for h in H]), dtype=np.float64) for i in range(4)]
         leaves = np.ascontiguousarray(robot.get_leaf_nodes(), dtype=np.int32)
         self.nleaf = len(leaves)

@@ -41,6 +41,14 @@ def test_emitted_bodies_match_reference_golden(name, golden, tmp_path):
         assert rel_err([lin[3 * n * n:]], [qdd_fd]) < 1e-9
         Ml = lin[2 * n * n:3 * n * n].reshape(n, n)
         assert np.array_equal(Ml, Ml.T)
+        # split (warp-specialised) forms: phase A + one function per derivative column on the published state
+        assert rel_err([call(lib, gen, "split_inverse_dynamics_gradient", 2 * n * n, q, qd)], [cm(g_["dc_du0"][k])]) < TOL
+        assert rel_err([call(lib, gen, "split_inverse_dynamics_gradient_qdd", 2 * n * n, q, qd, qdd)], [cm(g_["dc_du"][k])]) < TOL
+        assert rel_err([call(lib, gen, "split_forward_dynamics_gradient", 2 * n * n, q, qd, u)], [cm(g_["df_du"][k])]) < 1e-9
+        lin = call(lib, gen, "split_forward_dynamics_linearization", 3 * n * n + n, q, qd, u)
+        assert rel_err([lin[:2 * n * n]], [cm(g_["df_du"][k])]) < 1e-9
+        assert rel_err([lin[2 * n * n:3 * n * n]], [cm(Minv)]) < 1e-9
+        assert rel_err([lin[3 * n * n:]], [qdd_fd]) < 1e-9
         # qdd+Minv input mode: feeding the FD solution reproduces grad FD
         out = call(lib, gen, "forward_dynamics_gradient_qdd_minv", 2 * n * n, q, qd, qdd_fd, cm(Minv))
         assert rel_err([out], [cm(g_["df_du"][k])]) < 1e-9

@@ -1,0 +1,220 @@
+"""GPU parity at the sizes BASELINE.json's configs state (run with -m gpu on a B200).
+
+Small batches never reach the size-dependent code: the persistent grid runs more than one round per warp only above
+(resident CTAs x warps x 32) knots, the global-scratch state path (Atlas gradients) and the transposed-store path
+(second-order tensors, large matrices) reuse their scratch between rounds, and the host entry points cut the batch
+into chunks that rotate over three streams.  Each config therefore runs at its per-GPU size (and Atlas also at the
+whole 65536-knot batch on one GPU), checked on a seeded subsample of 512 first + 512 random knots against the pinned
+oracle, with guard bands around the output rows and with the host entry point compared with the
+device one.  Tolerances are north_star's: 1e-4 relative (fp32), metric conftest.rel_err.
+"""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL32 = 1e-4
+GUARD = 64
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    torch.cuda.set_device(0)
+    return torch
+
+
+def _lib(name):
+    import os
+    from gridcodegenerator_b200.runtime import get_library, library_path
+    if not os.path.exists(library_path(name)):
+        pytest.fail(f"libgrid_{name}.so was not prebuilt by build(); refusing to compile inside a GPU test")
+    return get_library(name)
+
+
+def _oracle(name):
+    from gridcodegenerator_b200.robot import load_robot
+    from oracle import Oracle
+    return Oracle(load_robot(name))
+
+
+def _subsample(rng, B, k=512):
+    k = min(k, B)
+    return np.unique(np.concatenate([np.arange(k), rng.choice(B, k, replace=False)]))
+
+
+def _guarded(torch, B, m):
+    buf = torch.full((GUARD + B * m + GUARD,), 12345.0, dtype=torch.float32, device="cuda")
+    return buf, buf[GUARD:GUARD + B * m].view(B, m)
+
+
+def _guards_intact(buf, B, m):
+    return bool((buf[:GUARD] == 12345.0).all()) and bool((buf[GUARD + B * m:] == 12345.0).all())
+
+
+def _check(torch, lib, method, X, m, ref_fn, idx, x32, tol=TOL32):
+    """Run `method` into a guarded buffer; compare the subsample with the oracle; return the output."""
+    B = X.shape[0]
+    buf, out = _guarded(torch, B, m)
+    getattr(lib, method)(X, out=out)
+    torch.cuda.synchronize()
+    assert _guards_intact(buf, B, m), f"{method}: wrote outside its rows"
+    assert bool(torch.isfinite(out).all()), method
+    got = out[torch.from_numpy(idx).cuda()].cpu().numpy().astype(np.float64)
+    err = rel_err(got, ref_fn(x32[idx].astype(np.float64)))
+    assert err < tol, (method, B, err)
+    return out
+
+
+def test_config2_iiwa14_mpc_horizon(torch_cuda):
+    """configs[1]: iiwa14 grad RNEA + direct Minv -> grad FD, batch 1024 (whole batch against the oracle)."""
+    torch = torch_cuda
+    lib, orc = _lib("iiwa14"), _oracle("iiwa14")
+    n, B = lib.n, 1024
+    rng = np.random.default_rng(2)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    X = torch.from_numpy(x32).cuda()
+    idx = np.arange(B)
+    _check(torch, lib, "forward_dynamics_gradient", X, 2 * n * n, orc.batch_fd_grad, idx, x32)
+    _check(torch, lib, "direct_minv", X[:, :n].contiguous(), n * n, orc.batch_minv, idx, x32)
+    _check(torch, lib, "inverse_dynamics_gradient", X[:, :2 * n].contiguous(), 2 * n * n,
+           lambda x: orc.batch_rnea_grad(x, use_qdd=False), idx, x32)
+
+
+def test_config3_hyq_16384(torch_cuda):
+    """configs[2]: HyQ grad FD + ABA, batch 16384.  grad FD of HyQ goes through the transposed-store scratch path;
+    the host entry point cuts the batch into two chunks on two streams (each owns its scratch)."""
+    torch = torch_cuda
+    lib, orc = _lib("hyq"), _oracle("hyq")
+    n, B = lib.n, 16384
+    rng = np.random.default_rng(3)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    X = torch.from_numpy(x32).cuda()
+    idx = _subsample(rng, B)
+    out = _check(torch, lib, "forward_dynamics_gradient", X, 2 * n * n, orc.batch_fd_grad, idx, x32)
+    _check(torch, lib, "aba", X, n, orc.batch_aba, idx, x32)
+    _check(torch, lib, "forward_dynamics_linearization", X, 3 * n * n + n,
+           lambda x: np.concatenate([orc.batch_fd_grad(x), orc.batch_minv(x), orc.batch_fd(x)], axis=1), idx, x32)
+    h = lib.forward_dynamics_gradient_host(torch.from_numpy(x32).pin_memory())
+    assert torch.equal(h, out.cpu()), "host entry point (chunked, 3 streams) differs from the device entry point"
+
+
+@pytest.mark.parametrize("B", [8192, 65536])
+def test_config4_atlas(B, torch_cuda):
+    """configs[3]: Atlas grad FD / CRBA / Minv at the per-GPU share of the 8-GPU run (8192) and at the whole batch on
+    one GPU (65536: more than one round per warp on the global-scratch state path)."""
+    torch = torch_cuda
+    lib, orc = _lib("atlas"), _oracle("atlas")
+    n = lib.n
+    rng = np.random.default_rng(4)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    X = torch.from_numpy(x32).cuda()
+    idx = _subsample(rng, B)
+    rounds = -(-(B // 32) // (lib.persistent_blocks("forward_dynamics_gradient") *
+                              (lib.kernel_info("forward_dynamics_gradient")["threads"] // 32)))
+    if B == 65536:
+        assert rounds >= 2, "the 65536-knot case must exercise scratch reuse across rounds"
+    out = _check(torch, lib, "forward_dynamics_gradient", X, 2 * n * n, orc.batch_fd_grad, idx, x32)
+    q = X[:, :n].contiguous()
+    _check(torch, lib, "crba", q, n * n, orc.batch_crba, idx, x32)
+    _check(torch, lib, "direct_minv", q, n * n, orc.batch_minv, idx, x32)
+    if B == 8192:
+        # 20000 knots = three chunks of the host pipeline in flight on three streams
+        Bh = 20000
+        xh = rng.uniform(-1, 1, (Bh, 3 * n)).astype(np.float32)
+        dev = lib.forward_dynamics_gradient(torch.from_numpy(xh).cuda()).cpu()
+        h = lib.forward_dynamics_gradient_host(torch.from_numpy(xh).pin_memory())
+        assert torch.equal(h, dev), "Atlas host entry point differs from the device entry point"
+    del out
+
+
+def test_config5_iiwa14_second_order_and_ee_32768(torch_cuda):
+    """configs[4]: iiwa14 IDSVA_SO / FDSVA_SO + EE pose gradient / Hessian at the per-GPU share (32768 of 262144):
+    several rounds of the transposed-store path.  Oracle: pinned to the reference-derived fixtures on the CPU
+    (tests/test_oracle_golden.py); its central differences are good to ~1e-7, far inside the fp32 tolerance."""
+    torch = torch_cuda
+    lib, orc = _lib("iiwa14"), _oracle("iiwa14")
+    assert lib.has_second_order and lib.has_ee_hessian
+    n, B = lib.n, 32768
+    rng = np.random.default_rng(5)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    X = torch.from_numpy(x32).cuda()
+    idx = _subsample(rng, B, 256)
+    _check(torch, lib, "idsva_so", X, 4 * n ** 3, orc.batch_idsva_so, idx, x32)
+    _check(torch, lib, "fdsva_so", X, 4 * n ** 3, orc.batch_fdsva_so, idx, x32)
+    q = X[:, :n].contiguous()
+    ne = lib.num_ees
+    _check(torch, lib, "end_effector_pose", q, 6 * ne, orc.batch_ee_pose, idx, x32)
+    # RPY derivatives grow like 1/cos(pitch)^k: compare the fp32 kernels with the fp64 kernels per knot, relative to
+    # the fp64 tensor's own scale, and the fp64 kernels with the oracle
+    g32, h32 = lib.end_effector_pose_gradient_hessian(q)
+    sel = torch.from_numpy(idx).cuda()
+    q64 = q[sel].double()
+    g64, h64 = lib.end_effector_pose_gradient_hessian(q64)
+    assert rel_err(g64.cpu().numpy(), orc.batch_ee_pose_gradient(x32[idx].astype(np.float64))) < 1e-7
+    assert rel_err(h64.cpu().numpy(), orc.batch_ee_pose_hessian(x32[idx].astype(np.float64))) < 1e-5
+    gs = g64.abs().amax(dim=1).clamp(min=1.0)
+    hs = h64.abs().amax(dim=1).clamp(min=1.0)
+    assert float(((g32[sel].double() - g64).abs().amax(dim=1) / gs).median()) < TOL32
+    assert float(((h32[sel].double() - h64).abs().amax(dim=1) / hs).median()) < TOL32
+
+
+@pytest.mark.parametrize("name,B", [("hyq", 4096), ("atlas", 1024)])
+def test_two_streams_do_not_share_scratch(name, B, torch_cuda):
+    """The device entry points are asynchronous on the caller's stream; kernels whose state / output staging lives
+    in the global scratch (HyQ and Atlas gradients) get one scratch per stream, so two streams may run them
+    concurrently (one scratch per device let the second stream's CTAs overwrite the first's)."""
+    torch = torch_cuda
+    lib = _lib(name)
+    n = lib.n
+    rng = np.random.default_rng(6)
+    xa = torch.from_numpy(rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)).cuda()
+    xb = torch.from_numpy(rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)).cuda()
+    ref_a = lib.forward_dynamics_gradient(xa)
+    ref_b = lib.forward_dynamics_gradient(xb)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(3):
+        outs = []
+        for s, x in ((s1, xa), (s2, xb), (s1, xb), (s2, xa)):
+            with torch.cuda.stream(s):
+                outs.append(lib.forward_dynamics_gradient(x))
+        torch.cuda.synchronize()
+        assert torch.equal(outs[0], ref_a) and torch.equal(outs[1], ref_b)
+        assert torch.equal(outs[2], ref_b) and torch.equal(outs[3], ref_a)
+
+
+def test_two_host_threads_two_devices(torch_cuda):
+    """One process, one host thread per device (SURVEY.md 8(b3) re-entrancy): results are bit-identical to the
+    single-device run.  Needs two GPUs (skipped on a one-GPU box; run under gpurun --gpus 2)."""
+    import threading
+    torch = torch_cuda
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    lib = _lib("hyq")
+    n, B = lib.n, 12000
+    rng = np.random.default_rng(7)
+    x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
+    ref = lib.forward_dynamics_gradient(torch.from_numpy(x32).cuda()).cpu()
+    res, errs = {}, []
+
+    def work(dev):
+        try:
+            torch.cuda.set_device(dev)
+            for _ in range(3):
+                d = lib.forward_dynamics_gradient(torch.from_numpy(x32).to(f"cuda:{dev}")).cpu()
+                h = lib.forward_dynamics_gradient_host(torch.from_numpy(x32).pin_memory())
+                res[dev] = (d, h.clone())
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    ts = [threading.Thread(target=work, args=(d,)) for d in (0, 1)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    torch.cuda.set_device(0)
+    assert not errs, errs
+    for dev in (0, 1):
+        assert torch.equal(res[dev][0], ref) and torch.equal(res[dev][1], ref), dev

@@ -65,3 +65,38 @@ def test_oracle_batch_layout(name, golden):
     assert rel_err(out, ref) < 1e-9
     out = orc.batch_minv(x, nthreads=1)
     assert rel_err(out, g["Minv"].reshape(len(x), -1)) < TOL
+
+
+@pytest.mark.parametrize("name", ["pendulum2", "chain3", "branched6", "iiwa14", "hyq"])
+def test_oracle_second_order_matches_reference_derivatives(name, golden):
+    """IDSVA_SO / FDSVA_SO: the reference has no executable CPU code for them, so the fixtures are the exact
+    (complex-step) derivatives of the reference's own test_rnea_grad / test_fd_grad / test_minv / test_rnea
+    (tools/make_golden.py).  The oracle's central differences of its pinned first-order functions must agree
+    to finite-difference accuracy."""
+    g = golden(name)
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    orc = Oracle(robot)
+    x = g["x"]
+    K2 = g["so_idsva"].shape[0]
+    xi = np.concatenate([x[:K2, :2 * n], x[:K2, 3 * n:4 * n]], axis=1)          # q | qd | qdd
+    assert rel_err(orc.batch_idsva_so(xi), g["so_idsva"].reshape(K2, -1)) < 1e-7
+    assert rel_err(orc.batch_fdsva_so(x[:K2, :3 * n]), g["so_fdsva"].reshape(K2, -1)) < 1e-6
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+def test_oracle_end_effector_matches_sympy_golden(name, golden):
+    """EE pose / gradient / Hessian of the oracle against the fixtures differentiated by sympy from the robot's
+    homogeneous transforms (reference algorithms/_eepose_gradient_hessian.py:150-157 pose formulas)."""
+    g = golden(name)
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    orc = Oracle(robot)
+    x = g["x"]
+    K = len(x)
+    ne = len(robot.get_leaf_nodes())
+    assert rel_err(orc.batch_ee_pose(x[:, :n]), g["ee_pose"]) < 1e-12
+    grad = orc.batch_ee_pose_gradient(x[:, :n]).reshape(K, ne, n, 6).transpose(0, 1, 3, 2).reshape(K, 6 * ne, n)
+    assert rel_err(grad, g["ee_grad"]) < 1e-7
+    if "ee_hess" in g:
+        assert rel_err(orc.batch_ee_pose_hessian(x[:, :n]), g["ee_hess"].reshape(K, -1)) < 1e-5
