@@ -36,7 +36,10 @@ class GRiDCodeGenerator:
         self.model = Model(robotObj)
         self._bodies: Dict[str, _algos.Body] = {}
         self._sbodies: Dict[str, _algos.SplitBody] = {}
-        self._specs = {sp.fn + sp.tag: sp for sp in _hdr.specs(self.model.n, robotObj.get_total_leaf_nodes())}
+        roots = [j for j in range(self.model.n) if self.model.parent[j] < 0]
+        self.max_tree = max(len(self.model.subtree[r]) for r in roots)      # joints of the largest base-rooted tree
+        self._specs = {sp.fn + sp.tag: sp
+                       for sp in _hdr.specs(self.model.n, robotObj.get_total_leaf_nodes(), self.max_tree)}
 
     # ------------------------------------------------- emission core (L1 API)
     # reference helpers/_code_generation_helpers.py:1-40 (same names, same behaviour)
@@ -73,9 +76,9 @@ class GRiDCodeGenerator:
         self.gen_add_code_line(" */")
 
     def _add_block(self, text: str):
+        # one append per block: code_str += per line is quadratic on a 16 MB header (Atlas: minutes)
         ind = "    " * self.indent_level
-        for line in text.split("\n"):
-            self.code_str += (ind + line if line else "") + "\n"
+        self.code_str += "".join((ind + line if line else "") + "\n" for line in text.split("\n"))
 
     # --------------------------------------------------------- body cache
     def _body(self, name: str) -> _algos.Body:
@@ -234,11 +237,12 @@ def gen_add_constants_helpers(self):
              "const int KNOTS_PER_WARP = 32;    // one lane owns one knot point",
              "const int SUGGESTED_THREADS = 32; // single-warp CTAs: warps never synchronise with each other"]
     per4, per8 = _scratch_constants(self)
-    lines += [f"#define GRID_HAS_SECOND_ORDER {int(_hdr.second_order_enabled(n))}",
+    lines += [f"#define GRID_HAS_SECOND_ORDER {int(_hdr.second_order_enabled(self.max_tree))}",
               f"#define GRID_HAS_EE_HESSIAN {int(_hdr.ee_hessian_enabled(n))}",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F64 = {per8};",
-              "const int GRID_SCRATCH_BLOCKS_PER_SM = 2;"]
+              # the scratch serves SMs x this many CTAs; one per SM when a slab would pass 1 GiB (fp32, 148 SMs)
+              f"const int GRID_SCRATCH_BLOCKS_PER_SM = {1 if per4 * 296 * 4 > (1 << 30) else 2};"]
     self.gen_add_code_lines(lines)
     self._add_block(_sc.STRUCTS)
 

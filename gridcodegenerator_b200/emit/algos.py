@@ -50,18 +50,23 @@ class Ctx:
         self.gravity = V(s="gravity")
 
     # -------------------------------------------------------------- inputs
-    def read_vec(self, ptr: str, prefix: str) -> List[V]:
-        return [self.em.named(f"{prefix}{j}", f"{ptr}[{j}]") for j in range(self.n)]
+    def read_vec(self, ptr: str, prefix: str, joints=None) -> List[V]:
+        """Named copies of a per-knot input vector (all joints, or only `joints`: None elsewhere)."""
+        return [self.em.named(f"{prefix}{j}", f"{ptr}[{j}]") if (joints is None or j in joints) else None
+                for j in range(self.n)]
 
-    def prologue(self, q_ptr: str = "q", seeded: bool = False):
+    def prologue(self, q_ptr: str = "q", seeded: bool = False, joints=None):
         """sin/cos of every revolute joint angle (reference helpers/_topology_helpers.py:194-195) and the
         factored transform handles.  With `seeded`, q_j is AD seed j: sin/cos (or q for prismatic joints) carry
         their first and second derivatives with respect to q_j (used when Em.ad_order > 0)."""
         em = self.em
-        self.q = self.read_vec(q_ptr, "q_")
-        self.X = []
-        self.trig = []
+        self.q = self.read_vec(q_ptr, "q_", joints)
+        if joints is None or not getattr(self, "X", None):
+            self.X = [None] * self.n
+            self.trig = [None] * self.n
         for j, jd in enumerate(self.m.joints):
+            if joints is not None and j not in joints:
+                continue
             if jd.revolute:
                 em.line(f"T sn{j}, cs{j}; grid_sincos(q_{j}, &sn{j}, &cs{j});")
                 sn, cs = V(s=f"sn{j}"), V(s=f"cs{j}")
@@ -74,8 +79,8 @@ class Ctx:
                 if seeded:
                     self.q[j] = V(s=self.q[j].s, d={j: ONE})
                 tr = Trig(None, None, self.q[j])
-            self.X.append(Xform(jd, tr))
-            self.trig.append((tr.s, tr.c, tr.q))
+            self.X[j] = Xform(jd, tr)
+            self.trig[j] = (tr.s, tr.c, tr.q)
 
     def seed_vec(self, vec: Sequence[V], first_seed: int) -> List[V]:
         """Mark vec[j] as AD seed first_seed + j."""
@@ -122,15 +127,18 @@ class Pusher:
 
 
 # ====================================================================== RNEA
-def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f"):
+def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f", joints=None):
     """v, a, f per joint in id order (ids are topologically sorted).  f_j -> state `fname`; with `keep`
-    also v_j, I v_j and X a_parent (needed by the gradient)."""
+    also v_j, I v_j and X a_parent (needed by the gradient).  `joints`: restrict to the joints of some base-rooted
+    trees (they do not interact with the rest of a fixed-base robot)."""
     em, m = cx.em, cx.m
     V_: Dict[int, List[V]] = {}
     A_: Dict[int, List[V]] = {}
     grav = [ZERO] * 5 + [cx.gravity]
     nonadj_parent = {p for j, p in enumerate(m.parent) if p >= 0 and p != j - 1}
     for j, jd in enumerate(m.joints):
+        if joints is not None and j not in joints:
+            continue
         em.comment(f"RNEA forward, joint {j}")
         p, S = jd.parent, jd.S
         if p >= 0:
@@ -168,7 +176,7 @@ def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: boo
         A_.pop(j - 2, None)
 
 
-def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f") -> List[V]:
+def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f", joints=None) -> List[V]:
     """f_parent += X^T f, c_j = S^T f_j + damping qd_j (reference _test.py:78-107)."""
     em, m = cx.em, cx.m
     ps = Pusher(em, fname)
@@ -176,6 +184,8 @@ def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f") -> L
         ps.in_state[j] = True
     c: List[V] = [ZERO] * m.n
     for j in range(m.n - 1, -1, -1):
+        if joints is not None and j not in joints:
+            continue
         jd = m.joints[j]
         em.comment(f"RNEA backward, joint {j}")
         f = ps.pull(j)
@@ -821,7 +831,7 @@ def body_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> Body:
     return Body("inverse_dynamics_gradient_inner", "", cx, "[dc/dq | dc/dqd], column-major n x 2n")
 
 
-def ltdl_factor(cx: Ctx, Mv: Dict[tuple, V]):
+def ltdl_factor(cx: Ctx, Mv: Dict[tuple, V], joints=None):
     """Sparse L^T D L factorisation of the joint-space inertia matrix (Featherstone RBDA table 6.3): M = L^T D L with
     L unit lower triangular and L[k][i] != 0 only for i an ancestor of k, so branch sparsity is kept.  Returns
     (L: dict (k, i) -> V, Dinv: list of V).  Used by grad FD to apply M^-1 without forming it: the reference
@@ -829,13 +839,14 @@ def ltdl_factor(cx: Ctx, Mv: Dict[tuple, V]):
     factor + solves give the same result in ~half the operations of the analytical Minv."""
     em, m, n = cx.em, cx.m, cx.n
     H: Dict[tuple, V] = {}
-    for i in range(n):
+    act = range(n) if joints is None else sorted(joints)
+    for i in act:
         H[(i, i)] = Mv[(i, i)]
         for j in m.ancestors[i]:
             H[(i, j)] = Mv[(min(i, j), max(i, j))]          # lower triangle, row i, column j = ancestor
     L: Dict[tuple, V] = {}
     Dinv: List[V] = [ZERO] * n
-    for k in range(n - 1, -1, -1):
+    for k in reversed(act):
         Dinv[k] = em.recip(H[(k, k)])
         i = m.parent[k]
         while i >= 0:
@@ -849,9 +860,28 @@ def ltdl_factor(cx: Ctx, Mv: Dict[tuple, V]):
     return L, Dinv
 
 
-def ltdl_solve(cx: Ctx, L, Dinv, b: Sequence[V], sign: float = 1.0) -> List[V]:
-    """x = sign * M^-1 b with M = L^T D L (b scalar- or pair-valued)."""
+def ltdl_solve(cx: Ctx, L, Dinv, b: Sequence[V], sign: float = 1.0, joints=None) -> List[V]:
+    """x = sign * M^-1 b with M = L^T D L (b scalar- or pair-valued).  With `joints` (whole base-rooted trees) only
+    that diagonal block is solved; the other entries of x are structural zeros."""
     em, m, n = cx.em, cx.m, cx.n
+    if joints is not None:
+        act = sorted(joints)
+        x = [b[i] if i in joints else ZERO for i in range(n)]
+        for i in reversed(act):
+            j = m.parent[i]
+            while j >= 0:
+                x[j] = em.lincomb([(1.0, x[j]), (-1.0, L[(i, j)], x[i])])
+                j = m.parent[j]
+        for i in act:
+            x[i] = em.lincomb([(sign, x[i], Dinv[i])])
+        for i in act:
+            j = m.parent[i]
+            terms = [(1.0, x[i])]
+            while j >= 0:
+                terms.append((-1.0, L[(i, j)], x[j]))
+                j = m.parent[j]
+            x[i] = em.lincomb(terms)
+        return x
     x = list(b)
     for i in range(n - 1, -1, -1):                      # x = L^-T b
         j = m.parent[i]
@@ -1041,7 +1071,7 @@ def body_aba(model: Model) -> Body:
 
 
 # ===================================================================== CRBA
-def crba_matrix(cx: Ctx) -> Dict[tuple, V]:
+def crba_matrix(cx: Ctx, joints=None) -> Dict[tuple, V]:
     """Joint-space inertia matrix M(q), full symmetric, column-major (reference algorithms/_crba.py:30-209;
     Featherstone RBDA table 6.2).  The composite inertia of joint j is final once all its descendants (ids > j,
     DFS pre-order) have been folded in, so column j of M is produced right there by walking f_h = IC_j S up the
@@ -1052,6 +1082,8 @@ def crba_matrix(cx: Ctx) -> Dict[tuple, V]:
     in_state: Dict[int, bool] = {}
     Mv: Dict[tuple, V] = {}
     for j in range(n - 1, -1, -1):
+        if joints is not None and j not in joints:
+            continue
         jd = m.joints[j]
         em.comment(f"CRBA, joint {j}")
         IC = [[const(jd.I[r, k]) for k in range(6)] for r in range(6)]
@@ -1320,29 +1352,48 @@ def body_end_effector_pose_gradient_hessian(model: Model) -> Body:
 
 # ============================================================ split (warp-specialised) bodies
 class SplitBody:
-    """One algorithm emitted as  phase A (first-order passes, one warp, publishes the per-knot state in shared memory)
+    """One algorithm emitted as  phase A (first-order passes; one function per PART = group of base-rooted trees of the
+    robot, the parts run concurrently on different warps and publish the per-knot state in shared memory)
     +  one function per derivative column (phase B: the columns of a tile run concurrently on the warps of the CTA).
 
     The per-knot state (v, Iv, X a_parent, f, L, 1/D, sin/cos, qd: 217 values for iiwa14) is what the reference
     keeps in shared memory between its __syncthreads phases (algorithms/_inverse_dynamics_gradient.py:27-140); here
     it is written once by phase A as S[slot*32 + lane] and read by the column functions."""
 
-    def __init__(self, name: str, cx: Ctx, doc: str, phase_a: Em, columns):
+    def __init__(self, name: str, cx: Ctx, doc: str, parts, columns):
         self.name, self.doc = name, doc
-        self.code = phase_a.code()
-        self.nslots = phase_a.nslots
-        self.n_ops = phase_a.n_ops + sum(e.n_ops for _, e in columns)
-        self.phase_a_ops = phase_a.n_ops
+        self.parts = parts                               # [(code, n_ops)] of phase A
+        self.code = "".join(c for c, _ in parts)
+        self.nslots = cx.em.nslots
+        self.phase_a_ops = max(o for _, o in parts)      # the parts run concurrently
+        self.n_ops = sum(o for _, o in parts) + sum(e.n_ops for _, e in columns)
         self.columns = [(c, e.code(), e.n_ops) for c, e in columns]
 
 
-def _publish_state(cx: Ctx, qd: Sequence[V], extra=()):
-    """End of phase A: make every value the column functions read a shared state slot.  Small robots run phase A
-    on SSA values (registers), so the values are stored now; big robots already keep them in slots."""
+def tree_parts(model: Model, max_parts: int = 4):
+    """Joint sets that phase A can process independently: the base-rooted trees of a fixed-base robot (HyQ: its four
+    legs; Atlas: torso + arms, left leg, right leg) do not interact in RNEA, CRBA or the factorisation.  Trees are
+    grouped into at most max_parts parts of similar size; a single tree gives [None] (= all joints)."""
+    if os.environ.get("GRID_SPLIT_TREE_PARTS", "1") == "0":
+        return [None]
+    roots = [j for j in range(model.n) if model.parent[j] < 0]
+    if len(roots) < 2:
+        return [None]
+    trees = sorted((sorted(model.subtree[r]) for r in roots), key=len, reverse=True)
+    parts = [[] for _ in range(min(max_parts, len(trees)))]
+    for t in trees:
+        min(parts, key=len).extend(t)
+    return [frozenset(p) for p in parts if p]
+
+
+def _publish_state(cx: Ctx, qd: Sequence[V], extra=(), joints=None):
+    """End of (a part of) phase A: make every value the column functions read a shared state slot.  Small robots run
+    phase A on SSA values (registers), so the values are stored now; big robots already keep them in slots."""
     em, m, n = cx.em, cx.m, cx.n
     em.comment("---- publish the per-knot state for the column functions")
+    act = [j for j in range(n) if joints is None or j in joints]
     keys = []
-    for j in range(n):
+    for j in act:
         for nm in ("v", "Iv", "Xa", "f"):
             keys += [(nm, j, k) for k in range(6)]
     keys += list(extra)
@@ -1355,7 +1406,7 @@ def _publish_state(cx: Ctx, qd: Sequence[V], extra=()):
         em.regs_only = False
     for key, v in pending:
         em.store(key, v)
-    for j in range(n):
+    for j in act:
         sn, cs, qv = cx.trig[j]
         if sn is not None:
             em.store(("sn", j, 0), V(s=sn.s))
@@ -1413,17 +1464,37 @@ def _split_columns(cx: Ctx, sink_factory):
     return cols
 
 
+def _begin_part(cx: Ctx):
+    """Start the function of the next phase-A part on the shared emitter: fresh text, NO reuse of state slots freed
+    by the previous part (the parts run concurrently), SSA mode as configured."""
+    em = cx.em
+    em.lines = []
+    em.free = []
+    em._out_acquired = False
+    em.regs_only = split_phase_a_regs_policy(cx.n)
+    return em.n_ops
+
+
+def _tree_of(model: Model, j: int):
+    """Joints of the base-rooted tree that contains joint j."""
+    r = min(model.ancestors[j]) if model.ancestors[j] else j
+    return frozenset(model.subtree[r])
+
+
 def split_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> SplitBody:
     cx = Ctx(model)
     em, n = cx.em, model.n
     em.no_sync = True
-    em.regs_only = split_phase_a_regs_policy(n)
-    cx.prologue()
-    qd = cx.read_vec("qd", "qd_")
-    qdd = cx.read_vec("qdd", "qdd_") if use_qdd else None
-    rnea_forward(cx, qd, qdd, keep=True)
-    rnea_backward(cx, qd, keep_f=True)
-    _publish_state(cx, qd)
+    parts = []
+    for js in tree_parts(model):
+        ops0 = _begin_part(cx)
+        cx.prologue(joints=js)
+        qd = cx.read_vec("qd", "qd_", js)
+        qdd = cx.read_vec("qdd", "qdd_", js) if use_qdd else None
+        rnea_forward(cx, qd, qdd, keep=True, joints=js)
+        rnea_backward(cx, qd, keep_f=True, joints=js)
+        _publish_state(cx, qd, joints=js)
+        parts.append((em.code(), em.n_ops - ops0))
 
     def sink_factory(cc):
         def sink(c, dc):
@@ -1434,52 +1505,64 @@ def split_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> SplitBody:
         return sink
 
     cols = _split_columns(cx, sink_factory)
-    return SplitBody("inverse_dynamics_gradient", cx, "[dc/dq | dc/dqd], column-major n x 2n", em, cols)
+    return SplitBody("inverse_dynamics_gradient", cx, "[dc/dq | dc/dqd], column-major n x 2n", parts, cols)
 
 
 def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -> SplitBody:
     """grad FD (optionally with the Minv and qdd side outputs) in split form: phase A = RNEA(q, qd, 0), CRBA,
-    L^T D L, qdd, RNEA(q, qd, qdd); phase B = one function per column c computing dc/dq_c, dc/dqd_c and the two
-    solves -M^-1 dc against the published factors."""
+    L^T D L, qdd, RNEA(q, qd, qdd), one part per group of base-rooted trees; phase B = one function per column c
+    computing dc/dq_c, dc/dqd_c and the two solves -M^-1 dc against the published factors."""
     cx = Ctx(model)
     em, n = cx.em, model.n
     em.no_sync = True
-    em.regs_only = split_phase_a_regs_policy(n)
-    cx.prologue()
-    qd = cx.read_vec("qd", "qd_")
-    u = cx.read_vec("u", "u_")
-    em.comment("---- phase A, pass 1: bias forces c = RNEA(q, qd, 0)")
-    rnea_forward(cx, qd, None, keep=False)
-    c = rnea_backward(cx, qd, keep_f=False)
-    em.comment("---- M = CRBA(q), M = L^T D L")
-    Mv = crba_matrix(cx)
-    L, Dinv = ltdl_factor(cx, Mv)
-    for k_, v_ in L.items():
-        em.store(("L",) + k_, v_)
-    for i_, v_ in enumerate(Dinv):
-        em.store(("Dinv2", i_, 0), v_)
-    qdd = ltdl_solve(cx, L, Dinv, [em.sub(u[j], c[j]) for j in range(n)])
-    if linearization:
-        em.comment("---- side outputs: Minv (dense symmetric, column-major) and qdd")
-        cols_ = [ltdl_solve(cx, L, Dinv, [ONE if r == k else ZERO for r in range(n)]) for k in range(n)]
-        for k in range(n):
-            for r in range(n):
-                _out(em, (2 * n + k) * n + r, cols_[k][r] if r <= k else cols_[r][k])
-        for j in range(n):
-            _out(em, 3 * n * n + j, qdd[j])
-    em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
-    rnea_forward(cx, qd, qdd, keep=True)
-    rnea_backward(cx, qd, keep_f=True)
-    lkeys = [("L",) + k_ for k_ in L] + [("Dinv2", i_, 0) for i_ in range(n)]
-    _publish_state(cx, qd, extra=lkeys)
+    parts = []
+    L_all: Dict[tuple, V] = {}
+    for js in tree_parts(model):
+        ops0 = _begin_part(cx)
+        act = list(range(n)) if js is None else sorted(js)
+        cx.prologue(joints=js)
+        qd = cx.read_vec("qd", "qd_", js)
+        u = cx.read_vec("u", "u_", js)
+        em.comment("---- phase A, pass 1: bias forces c = RNEA(q, qd, 0)")
+        rnea_forward(cx, qd, None, keep=False, joints=js)
+        c = rnea_backward(cx, qd, keep_f=False, joints=js)
+        em.comment("---- M = CRBA(q), M = L^T D L")
+        Mv = crba_matrix(cx, joints=js)
+        L, Dinv = ltdl_factor(cx, Mv, joints=js)
+        for k_, v_ in L.items():
+            em.store(("L",) + k_, v_)
+        for i_ in act:
+            em.store(("Dinv2", i_, 0), Dinv[i_])
+        L_all.update(L)
+        rhs = [em.sub(u[j], c[j]) if j in act else ZERO for j in range(n)]
+        qdd = ltdl_solve(cx, L, Dinv, rhs, joints=frozenset(act))
+        if linearization:
+            em.comment("---- side outputs: Minv (dense symmetric, column-major) and qdd")
+            cols_ = {k: ltdl_solve(cx, L, Dinv, [ONE if r == k else ZERO for r in range(n)], joints=frozenset(act))
+                     for k in act}
+            for k in act:
+                for r in range(n):
+                    # one value per symmetric pair, so that the stored matrix is exactly symmetric; entries between
+                    # different trees are structural zeros
+                    val = (cols_[k][r] if r <= k else cols_[r][k]) if r in cols_ else ZERO
+                    _out(em, (2 * n + k) * n + r, val)
+            for j in act:
+                _out(em, 3 * n * n + j, qdd[j])
+        em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
+        rnea_forward(cx, qd, qdd, keep=True, joints=js)
+        rnea_backward(cx, qd, keep_f=True, joints=js)
+        lkeys = [("L",) + k_ for k_ in L] + [("Dinv2", i_, 0) for i_ in act]
+        _publish_state(cx, qd, extra=lkeys, joints=js)
+        parts.append((em.code(), em.n_ops - ops0))
 
     def sink_factory(cc):
         def sink(c_, dc):
             e = cc.em
-            Ll = {k_: e.load(("L",) + k_) for k_ in L}
-            Dl = [e.load(("Dinv2", i_, 0)) for i_ in range(n)]
+            tree = _tree_of(model, c_)
+            Ll = {k_: e.load(("L",) + k_) for k_ in L_all if k_[0] in tree}
+            Dl = [e.load(("Dinv2", i_, 0)) if i_ in tree else ZERO for i_ in range(n)]
             for h in (0, 1):
-                x = ltdl_solve(cc, Ll, Dl, [_halves(e, d_)[h] for d_ in dc], sign=-1.0)
+                x = ltdl_solve(cc, Ll, Dl, [_halves(e, d_)[h] for d_ in dc], sign=-1.0, joints=tree)
                 for r in range(n):
                     _out(e, (h * n + c_) * n + r, x[r])
         return sink
@@ -1487,5 +1570,5 @@ def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -
     cols = _split_columns(cx, sink_factory)
     if linearization:
         return SplitBody("forward_dynamics_linearization", cx,
-                         "[dqdd/dq | dqdd/dqd | Minv | qdd]: grad FD with its Minv and qdd by-products", em, cols)
-    return SplitBody("forward_dynamics_gradient", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]", em, cols)
+                         "[dqdd/dq | dqdd/dqd | Minv | qdd]: grad FD with its Minv and qdd by-products", parts, cols)
+    return SplitBody("forward_dynamics_gradient", cx, "[dqdd/dq | dqdd/dqd] = -Minv [dc/dq | dc/dqd]", parts, cols)

@@ -37,8 +37,10 @@ class AlgoSpec:
     extra_kernel_params: str = ""
 
 
-def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
+def specs(n: int, num_ees: int = 1, max_tree: Optional[int] = None) -> List[AlgoSpec]:
+    """max_tree: joints of the largest base-rooted tree of the robot (default n: one tree)."""
     ee = num_ees
+    max_tree = n if max_tree is None else max_tree
     return [
         AlgoSpec("end_effector_pose", "end_effector_pose", "EE", "", algos.body_end_effector_pose,
                  ["q"], [("d_q", n)], [(0, 0)], "d_eePos", lambda n: 6 * ee, uses_gravity=False),
@@ -88,7 +90,7 @@ def specs(n: int, num_ees: int = 1) -> List[AlgoSpec]:
         AlgoSpec("fdsva_so", "fdsva_so", "FDSVA_SO", "", algos.body_fdsva_so,
                  ["q", "qd", "u"], [("d_q_qd_u", 3 * n)], [(0, 0), (0, n), (0, 2 * n)], "d_df2",
                  lambda n: 4 * n * n * n),
-    ] if second_order_enabled(n) else [])
+    ] if second_order_enabled(max_tree) else [])
 
 
 def ee_hessian_enabled(n: int) -> bool:
@@ -97,11 +99,14 @@ def ee_hessian_enabled(n: int) -> bool:
     return n <= int(os.environ.get("GRID_EE_HESSIAN_MAX_JOINTS", "16"))
 
 
-def second_order_enabled(n: int) -> bool:
-    """The second-order kernels are emitted by differentiating the straight-line RNEA / CRBA at emit time; their
-    code size grows ~n^3, so they are generated for robots up to SECOND_ORDER_MAX_JOINTS joints (the reference
-    likewise switches strategy above 8-10 joints: _idsva_so.py:1, _fdsva_so.py:1)."""
-    return n <= int(os.environ.get("GRID_SECOND_ORDER_MAX_JOINTS", "8"))
+def second_order_enabled(max_tree: int) -> bool:
+    """The second-order kernels are emitted by differentiating the straight-line RNEA / CRBA at emit time.  A
+    quantity only carries tangents for the joints it depends on, so the code grows with the cube of the largest
+    base-rooted TREE, not of the joint count: HyQ (12 joints, four 3-joint legs) is a third of iiwa14's code.  They
+    are generated for robots whose largest tree has at most SECOND_ORDER_MAX_JOINTS joints (the reference likewise
+    switches strategy above 8-10 joints: _idsva_so.py:1, _fdsva_so.py:1); results go straight to global memory
+    (transposed-store path) whatever n is, as the reference does for large n (_fdsva_so.py:205-210)."""
+    return max_tree <= int(os.environ.get("GRID_SECOND_ORDER_MAX_JOINTS", "8"))
 
 
 def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
@@ -201,14 +206,16 @@ def split_body(sp: AlgoSpec, model: Model) -> "algos.SplitBody":
 
 
 def split_assign(sb: "algos.SplitBody", max_warps: int = 0):
-    """Columns -> warps, longest-processing-time first.  The number of warps is the smallest that brings the
-    heaviest warp within 5 % of the heaviest single column (more warps cannot shorten phase B), at most
-    SPLIT_MAX_WARPS.  Returns a list (one entry per warp) of column lists."""
+    """Columns -> warps, longest-processing-time first.  Warp counts are multiples of four (registers are partitioned
+    per scheduler, ceil(warps / 4) warps each); the smallest count is taken whose heaviest warp is within 10 % of the
+    heaviest single column (more warps cannot shorten phase B) or below 30 % of phase A (phase B no longer matters):
+    small CTAs leave room for several CTAs per SM (measured on B200, profiles/r02a_tune_variants.log: iiwa14 with 4
+    warps 12.3 us at 8192 knots against 22.7 us with 8).  Returns a list (one entry per warp) of column lists."""
     max_warps = max_warps or SPLIT_MAX_WARPS
     cols = sorted(((ops, c) for c, _, ops in sb.columns), reverse=True)
     forced = os.environ.get("GRID_SPLIT_WARPS", "")
     best = None
-    for nw in ([int(forced)] if forced else range(1, max_warps + 1)):
+    for nw in ([int(forced)] if forced else range(4, max_warps + 1, 4)):
         load = [0] * nw
         groups = [[] for _ in range(nw)]
         for ops, c in cols:
@@ -216,9 +223,16 @@ def split_assign(sb: "algos.SplitBody", max_warps: int = 0):
             load[w] += ops
             groups[w].append(c)
         best = groups
-        if max(load) <= 1.05 * cols[0][0]:
+        if max(load) <= max(1.10 * cols[0][0], 0.30 * sb.phase_a_ops):
             break
     return [sorted(g) for g in best if g]
+
+
+def split_maxnreg(nw: int) -> int:
+    """Largest register budget per thread that lets one CTA of nw warps launch: each of the SM's four schedulers
+    owns 16384 registers and hosts ceil(nw / 4) of the CTA's warps."""
+    per_sched = -(-nw // 4)
+    return min(255, (16384 // (per_sched * 32)) // 8 * 8)
 
 
 def split_out_staged(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> bool:
@@ -234,17 +248,21 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     ins = "".join(f"const T* __restrict__ {p}, " for p in sp.inner_inputs)
     grav = "const T gravity" if sp.uses_gravity else "const T /*gravity*/"
     pre = "    using grid_rt::grid_sincos;\n    typedef grid_rt::pair_t<T> P;\n"
-    out = [f"/**\n * {sb.doc} -- SPLIT form, phase A: the first-order passes of one knot per lane; publishes the per-knot\n"
-           f" * state as S[slot*NT] ({sb.nslots} slots).  Emitted operations (mul+add): {sb.phase_a_ops}\n */\n"
-           f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
-           f"void {stem}_phaseA(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n" + pre + sb.code + "}\n\n"]
+    out = []
+    for p_, (code, ops) in enumerate(sb.parts):
+        out.append(f"/**\n * {sb.doc} -- SPLIT form, phase A, part {p_} of {len(sb.parts)} (parts = groups of base-rooted trees;\n"
+                   f" * they run concurrently on different warps): the first-order passes of one knot per lane; publishes the\n"
+                   f" * per-knot state as S[slot*NT] ({sb.nslots} slots in all).  Emitted operations (mul+add): {ops}\n */\n"
+                   f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
+                   f"void {stem}_phaseA{p_}(T* __restrict__ o, {ins}T* __restrict__ S, {grav}) {{\n" + pre + code + "}\n\n")
     for c, code, ops in sb.columns:
         out.append(f"/** SPLIT form, derivative column {c} (dq_{c} and dqd_{c}) of {sp.fn}: reads the published state, "
                    f"writes its output entries.  Emitted operations: {ops} */\n"
                    f"template <typename T, int NT, int OS = 1>\n__device__ __forceinline__\n"
                    f"void {stem}_col{c}(T* __restrict__ o, T* __restrict__ S) {{\n" + pre + code + "}\n\n")
     groups = split_assign(sb)
-    nw = len(groups)
+    na = len(sb.parts)
+    nw = max(len(groups), na)
     IN = [e for _, e in sp.streams] + [0, 0, 0]
     args = []
     for (s_, off) in sp.split:
@@ -259,12 +277,14 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
                f"    static constexpr int OUT = {sp.out_n(n)};\n"
                f"    static constexpr int SLOTS = {max(sb.nslots, 1)};\n"
                f"    static constexpr int NW = {nw};          // warps per CTA = column groups of phase B\n"
-               f"    static constexpr int NA = 1;           // warps running phase A\n"
+               f"    static constexpr int NA = {na};           // warps running phase A (one part each)\n"
                f"    static constexpr bool PHASE_A_WRITES = {'true' if writes else 'false'};\n"
                f"    template <int NT, int OS>\n"
-               f"    static __device__ __forceinline__ void phaseA(int /*warp*/, T* __restrict__ o, const T* __restrict__ x0, "
+               f"    static __device__ __forceinline__ void phaseA(int warp, T* __restrict__ o, const T* __restrict__ x0, "
                f"const T* __restrict__ x1, const T* __restrict__ x2, T* __restrict__ S, const T gravity) {{\n"
-               f"        {stem}_phaseA<T, NT, OS>(o, {', '.join(args)}, S, gravity);\n    }}\n"
+               f"        switch (warp) {{\n" + "\n".join(
+                   f"            case {p_}: {stem}_phaseA{p_}<T, NT, OS>(o, {', '.join(args)}, S, gravity); break;"
+                   for p_ in range(na)) + "\n            default: break;\n        }\n    }\n"
                f"    template <int NT, int OS>\n"
                f"    static __device__ __forceinline__ void phaseB(int warp, T* __restrict__ o, T* __restrict__ S) {{\n"
                f"        switch (warp) {{\n" + "\n".join(cases) + "\n            default: break;\n        }\n    }\n};\n\n")
@@ -288,7 +308,7 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
         fill.append(f"    a.in[{i}] = nullptr; a.stride[{i}] = 0;")
     gv = "gravity" if sp.uses_gravity else "T(0)"
     C = f"{stem}_cfg<T>"
-    bounds = (f"__maxnreg__({regs})" if regs else f"__maxnreg__(({C}::NT * 255 <= 65536) ? 255 : (65536 / {C}::NT / 8 * 8))")
+    bounds = f"__maxnreg__({regs or split_maxnreg(nw)})"
     out.append(f"template <typename T>\n__global__ void {bounds}\n"
                f"{sp.fn}_split_kernel({kernel_params(sp)}) {{\n"
                f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"

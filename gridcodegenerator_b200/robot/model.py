@@ -239,6 +239,32 @@ def _axis_index(axis: Sequence[float], name: str) -> int:
     )
 
 
+def _axis_frame(axis: Sequence[float], name: str) -> Tuple[int, np.ndarray]:
+    """(k, Q): principal index k and the coordinate rotation Q with Q @ axis = e_k.  The reference requires one-hot
+    motion subspaces (helpers/_spatial_algebra_helpers.py:13); a joint about any other axis -- negative principal
+    axes are common in real URDFs -- gets its joint frame re-oriented by Q (and the child link's frame by Q^T), which
+    leaves the kinematics and dynamics in terms of q unchanged."""
+    a = np.asarray(axis, dtype=np.float64)
+    nrm = float(np.linalg.norm(a))
+    if nrm < 1e-12:
+        raise ValueError(f"joint {name}: zero axis")
+    a = a / nrm
+    k = int(np.argmax(np.abs(a)))
+    e = np.zeros(3)
+    e[k] = 1.0
+    if np.allclose(a, e, atol=1e-12):
+        return k, np.eye(3)
+    if np.allclose(a, -e, atol=1e-12):
+        Q = -np.eye(3)
+        Q[(k + 1) % 3, (k + 1) % 3] = 1.0          # half turn about the next principal axis
+        return k, Q
+    # general axis: Rodrigues rotation about a x e_k taking a onto e_k
+    v = np.cross(a, e)
+    s_, c_ = float(np.linalg.norm(v)), float(a @ e)
+    K = np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]]) / s_
+    return k, np.eye(3) + s_ * K + (1.0 - c_) * (K @ K)
+
+
 def _compose(E1, r1, E2, r2):
     """Frame A->B (E1, r1) followed by B->C (E2, r2) gives A->C."""
     return spx.snap(E2 @ E1), spx.snap(r1 + E1.T @ r2)
@@ -284,11 +310,12 @@ class Robot:
                 Ej, rj = _compose(E, r, spx.rpy_to_E(jd.rpy), np.asarray(jd.xyz, dtype=np.float64))
                 if jd.jtype in _MOVABLE:
                     jid = len(self.joints)
-                    joint = Joint(jd, jid, body_id, Ej, rj, _axis_index(jd.axis, jd.name))
+                    k, Q = _axis_frame(jd.axis, jd.name)
+                    joint = Joint(jd, jid, body_id, spx.snap(Q @ Ej), rj, k)
                     self.joints.append(joint)
                     body_I[jid] = np.zeros((6, 6))
                     body_name[jid] = jd.child
-                    visit(jd.child, jid, np.eye(3), np.zeros(3))
+                    visit(jd.child, jid, spx.snap(Q.T), np.zeros(3))
                 elif jd.jtype == "fixed":
                     self.fixed_joints.append(FixedJoint(jd.name, len(self.fixed_joints), jd.parent, body_id, Ej, rj))
                     visit(jd.child, body_id, Ej, rj)

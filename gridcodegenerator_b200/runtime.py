@@ -245,7 +245,9 @@ class GRiDLibrary:
             raise RuntimeError("device entry points need CUDA tensors (no CPU fallback exists)")
         if t.dim() != 2 or t.stride(1) != 1 or t.shape[1] < cols_min:
             raise ValueError(f"expected a (B, >={cols_min}) row-major tensor, got {tuple(t.shape)} strides {t.stride()}")
-        return t.data_ptr(), int(t.stride(0)), int(t.shape[0])
+        # a one-row tensor has no meaningful row stride (torch keeps whatever the parent had)
+        stride = int(t.stride(0)) if t.shape[0] > 1 else int(t.shape[1])
+        return t.data_ptr(), stride, int(t.shape[0])
 
     @staticmethod
     def _out(out, like, B: int, m: int):

@@ -58,15 +58,17 @@ def build_host_inners(robot, workdir=None, second_order=False):
             stem = f"{sp.fn}{sp.tag}_split"
             pre = "    using grid_rt::grid_sincos;\n    typedef grid_rt::pair_t<T> P;\n"
             params = "".join(f"const T* {p}, " for p in sp.inner_inputs)
-            src.append(f"template <typename T, int NT, int OS = 1>\nvoid {stem}_phaseA(T* o, {params}T* S, const T gravity) {{\n"
-                       + pre + sb.code + "}\n")
+            for p_, (pcode, _) in enumerate(sb.parts):
+                src.append(f"template <typename T, int NT, int OS = 1>\nvoid {stem}_phaseA{p_}(T* o, {params}T* S, const T gravity) {{\n"
+                           + pre + pcode + "}\n")
             for c, code, _ in sb.columns:
                 src.append(f"template <typename T, int NT, int OS = 1>\nvoid {stem}_col{c}(T* o, T* S) {{\n" + pre + code + "}\n")
             cols = "".join(f"    {stem}_col{c}<double, 1>(o, S);\n" for c, _, _ in sb.columns)
             wrappers.append(
                 f'extern "C" void host_split_{name}(double* o, {ins}, double gravity) {{\n'
                 f"    static thread_local double S[{max(sb.nslots, 1)}];\n"
-                f"    {stem}_phaseA<double, 1>(o, {call}, S, gravity);\n{cols}}}\n")
+                + "".join(f"    {stem}_phaseA{p_}<double, 1>(o, {call}, S, gravity);\n" for p_ in range(len(sb.parts)))
+                + f"{cols}}}\n")
     text = "\n".join(src) + "\n".join(wrappers)
     workdir = workdir or tempfile.mkdtemp(prefix="grid_host_")
     cpp = os.path.join(workdir, f"inner_{robot.name}.cpp")

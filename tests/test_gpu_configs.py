@@ -155,7 +155,9 @@ def test_config5_iiwa14_second_order_and_ee_32768(torch_cuda):
     q64 = q[sel].double()
     g64, h64 = lib.end_effector_pose_gradient_hessian(q64)
     assert rel_err(g64.cpu().numpy(), orc.batch_ee_pose_gradient(x32[idx].astype(np.float64))) < 1e-7
-    assert rel_err(h64.cpu().numpy(), orc.batch_ee_pose_hessian(x32[idx].astype(np.float64))) < 1e-5
+    # the oracle's Hessian is a SECOND central difference (error ~1e-5 near the RPY singularity); the kernels' exact
+    # Hessian is pinned at 1e-9 against the sympy fixtures in test_gpu_parity.py::test_golden_vectors
+    assert rel_err(h64.cpu().numpy(), orc.batch_ee_pose_hessian(x32[idx].astype(np.float64))) < 1e-4
     gs = g64.abs().amax(dim=1).clamp(min=1.0)
     hs = h64.abs().amax(dim=1).clamp(min=1.0)
     assert float(((g32[sel].double() - g64).abs().amax(dim=1) / gs).median()) < TOL32

@@ -255,7 +255,8 @@ def test_end_effector_pose_gradient_hessian(name, B, torch_cuda):
 
 def test_second_order_absent_for_large_robots(torch_cuda):
     torch = torch_cuda
-    lib = _lib("hyq")
+    assert _lib("hyq").has_second_order          # 12 joints but four 3-joint trees: generated
+    lib = _lib("atlas")                           # largest base-rooted tree has 18 joints: not generated
     assert not lib.has_second_order
     x = torch.zeros((4, 3 * lib.n), dtype=torch.float32, device="cuda")
     with pytest.raises(RuntimeError, match="second-order"):

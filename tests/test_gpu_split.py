@@ -64,7 +64,7 @@ def test_split_form_fp32(name, B, torch_cuda):
     rng = np.random.default_rng(31)
     x32 = rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)
     X = torch.from_numpy(x32).cuda()
-    q_qd, qdd = X[:, :2 * n].contiguous(), X[:, 2 * n:].contiguous()
+    q_qd, qdd = X[:, :2 * n].contiguous(), X[:, 2 * n:].clone().reshape(B, n)
     idx = np.unique(np.concatenate([np.arange(min(B, 256)), rng.choice(B, min(B, 256), replace=False)]))
     sel = torch.from_numpy(idx).cuda()
     x64 = x32[idx].astype(np.float64)
