@@ -42,7 +42,7 @@ def _nvcc() -> str:
 def _source_digest(header_text: str) -> str:
     h = hashlib.sha256()
     h.update(header_text.encode())
-    for fn in ("grid_capi.cu",):
+    for fn in ("grid_capi.cu", "grid_noalloc.cu"):
         with open(os.path.join(CSRC, fn), "rb") as f:
             h.update(f.read())
     with open(os.path.join(INCLUDE, "grid_b200.h"), "rb") as f:
@@ -98,6 +98,20 @@ def _compile_part(name: str, out_dir: str, part: int, dtypes: int, verbose: bool
     return obj
 
 
+def _compile_noalloc(name: str, out_dir: str, verbose: bool) -> str:
+    """csrc/grid_noalloc.cu: the allocation-free grad-FD entry point with its static device scratch (one more
+    translation unit of the same library)."""
+    obj = os.path.join(out_dir, "noalloc.o")
+    cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f != "-shared"] + [
+        "-c", f"-I{out_dir}", f"-I{INCLUDE}", os.path.join(CSRC, "grid_noalloc.cu"), "-o", obj]
+    if verbose:
+        cmd[1:1] = ["-Xptxas", "-v"]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for robot {name}, grid_noalloc.cu:\n{res.stdout[-4000:]}")
+    return obj
+
+
 def build_library(robot, force: bool = False, verbose: bool = False, pool=None) -> str:
     """Emit grid.cuh for `robot` (a robot object or the name of a shipped robot) and compile the C-ABI
     library for sm_100a.  Returns the .so path.  Up-to-date builds are reused (digest of all sources).
@@ -112,17 +126,19 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
     gen = GRiDCodeGenerator(robot)
     gen.gen_all_code(output_dir=out_dir)
     digest = _source_digest(gen.code_str)
+    pkg_digest = _package_digest()          # taken BEFORE compiling: edits made during a long build must not be stamped
     so = library_path(name)
     stamp = os.path.join(out_dir, "digest.txt")
     if not force and os.path.exists(so) and os.path.exists(stamp) and open(stamp).read().strip() == digest:
         with open(os.path.join(out_dir, "package_digest.txt"), "w") as f:     # same header => binary still current
-            f.write(_package_digest())
+            f.write(pkg_digest)
         return so
     own = pool is None
     if own:
         pool = ThreadPoolExecutor(max_workers=min(len(CAPI_PARTS), os.cpu_count() or 1))
     try:
         futs = [pool.submit(_compile_part, name, out_dir, part, dt, verbose) for part, dt in CAPI_PARTS]
+        futs.append(pool.submit(_compile_noalloc, name, out_dir, verbose))
         objs = [f.result() for f in futs]
     finally:
         if own:
@@ -136,7 +152,7 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
     with open(stamp, "w") as f:
         f.write(digest)
     with open(os.path.join(out_dir, "package_digest.txt"), "w") as f:
-        f.write(_package_digest())
+        f.write(pkg_digest)
     return so
 
 

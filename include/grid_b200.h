@@ -151,6 +151,23 @@ int grid_inverse_dynamics_host_f32(const float *h_q_qd_u, float *h_c, int num_kn
 /* release the cached device workspace of the host entry points and the robot model handles */
 int grid_release(void);
 
+/* ---- grad FD without any allocation
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs / outputs / arithmetic as grid_forward_dynamics_gradient_f32 (one-lane-per-knot kernel form), but the
+ * kernel's global scratch is a file-scope static __device__ array of the library (csrc/grid_noalloc.cu) instead of a
+ * cudaMalloc'ed robot-model handle: no cudaMalloc / cudaFree / allocating library call at set-up or per call.
+ *   - limit: num_knots <= GRID_NOALLOC_MAX_KNOTS; larger batches return cudaErrorInvalidValue (see grid_last_error()).
+ *   - cost: every GPU that loads the library holds grid_noalloc_scratch_bytes() of device memory until exit
+ *     (HyQ 7 MB, Atlas 17 MB, robots whose grad FD needs no scratch 256 B); at most 32 CTAs run.
+ *   - every call on a device shares that one array (it keeps the previous call's contents; nothing in it has to start
+ *     at zero): calls that OVERLAP on the GPU -- two streams, two host threads on one device -- race; serialise them. */
+#define GRID_NOALLOC_MAX_KNOTS 8192
+int grid_forward_dynamics_gradient_noalloc_f32(const float *d_q_qd_u, int stride, float *d_df_du, int num_knots,
+                                               float gravity, void *stream);
+int grid_noalloc_max_knots(void);
+long grid_noalloc_scratch_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif
