@@ -1,8 +1,12 @@
 #!/bin/bash
 # round 2, GPU call b: full parity suite with the tree-parallel split kernels, form A/B for all robots, ncu reconciliation
 mkdir -p gpurun_out
+# the allocation-free entry point alone in a fresh process, then the whole suite (which ends with it)
+python -m pytest tests/test_zz_no_alloc.py -m gpu -q -p no:cacheprovider > gpurun_out/r02b_pytest_noalloc_alone.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02b_pytest_noalloc_alone.log
+tail -4 gpurun_out/r02b_pytest_noalloc_alone.log
 python -m pytest tests -m gpu -q -p no:cacheprovider > gpurun_out/r02b_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r02b_pytest.log
 tail -15 gpurun_out/r02b_pytest.log
+./tools/probes/rf_ports > gpurun_out/r02b_rf_ports.log 2>&1
 timeout 900 python tools/tune_split.py iiwa14 hyq atlas hyq:inverse_dynamics_gradient atlas:forward_dynamics_linearization > gpurun_out/r02b_tune_split.log 2>&1
 cat gpurun_out/r02b_tune_split.log | cut -c1-220
 timeout 600 python tools/bench_configs.py > gpurun_out/r02b_configs.log 2>&1; tail -30 gpurun_out/r02b_configs.log | cut -c1-250
