@@ -23,7 +23,7 @@ _CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 class GRiDCodeGenerator:
     # ------------------------------------------------------------------ ctor
     def __init__(self, robotObj, DEBUG_MODE=False, NEED_PRINT_MAT=False, USE_DYNAMIC_SHARED_MEM=True,
-                 FILE_NAMESPACE="grid"):
+                 FILE_NAMESPACE="grid", fixed_target_name=""):
         self.robot = robotObj
         self.code_str = ""
         self.indent_level = 0
@@ -38,8 +38,17 @@ class GRiDCodeGenerator:
         self._sbodies: Dict[str, _algos.SplitBody] = {}
         roots = [j for j in range(self.model.n) if self.model.parent[j] < 0]
         self.max_tree = max(len(self.model.subtree[r]) for r in roots)      # joints of the largest base-rooted tree
+        self._set_fixed_target(fixed_target_name or "")
+
+    def _set_fixed_target(self, name: str):
+        """Fixed kinematic target (a fixed joint of the robot) for which the additional single-target EE functions
+        are generated (reference gen_all_code(fixed_target_name=...), GRiDCodeGenerator.py:309-310, :417)."""
+        if name:
+            self.robot.get_fixed_joint_by_name(name)          # raises for an unknown name
+        self.fixed_target_name = name
+        self.include_fixed_kinematic_targets = name != ""
         self._specs = {sp.fn + sp.tag: sp
-                       for sp in _hdr.specs(self.model.n, robotObj.get_total_leaf_nodes(), self.max_tree)}
+                       for sp in _hdr.specs(self.model.n, self.robot.get_total_leaf_nodes(), self.max_tree, name)}
 
     # ------------------------------------------------- emission core (L1 API)
     # reference helpers/_code_generation_helpers.py:1-40 (same names, same behaviour)
@@ -101,6 +110,20 @@ class GRiDCodeGenerator:
             self._add_block(_hdr.emit_inner(sp, b))
             self._add_block(_hdr.emit_algo_struct(sp, b, self.model.n))
             self._add_block(_hdr.emit_config(sp, b, self.model.n))
+            if sp.fn == "joint_transforms":
+                # the reference's helper names for the same quantity (algorithms/_eepose_gradient_hessian.py:1226-1398)
+                self._add_block(
+                    "/** Local homogeneous transforms Xhom_j(q_j) -> s_XmatsHom and cumulative transforms base <- joint j\n"
+                    " *  -> s_jointXforms for every joint id <= tid (16 values each, column-major), in one thread. */\n"
+                    "template <typename T>\n__device__\nvoid X_single_thread(T *s_jointXforms, T *s_XmatsHom, const T *s_q, int tid) {\n"
+                    "    using grid_rt::grid_sincos;\n    constexpr int OS = 1;\n"
+                    + _algos.code_X_single_thread(self.model) + "}\n\n"
+                    "/** Same result with the reference's warp-level entry point: in this back end one lane owns one knot point,\n"
+                    " *  so lane 0 of the calling warp runs the chain and the warp re-converges. */\n"
+                    "template <typename T>\n__device__ inline void X_warp(T* __restrict__ s_jointXforms, T* __restrict__ s_XmatsHom,\n"
+                    "                              const T* __restrict__ s_q, int tid) {\n"
+                    "    if ((threadIdx.x & 31) == 0) X_single_thread<T>(s_jointXforms, s_XmatsHom, s_q, tid);\n"
+                    "    __syncwarp();\n}\n")
             if _hdr.has_split(sp, self.model.n):
                 # second form of the same algorithm: phase A on one warp, derivative columns spread over the CTA's warps
                 if v not in self._sbodies:
@@ -117,8 +140,8 @@ class GRiDCodeGenerator:
             self._add_block(_hdr.emit_launch(self._specs[v], self.model.n))
 
     def _gen_host(self, key: str, mode: int = 0):
-        for hs in _hdr.host_specs(self.model.n):
-            if hs.fn == key:
+        for hs in _hdr.host_specs(self.model.n, self.fixed_target_name):
+            if (hs.key or hs.fn) == key:
                 self._add_block(_hdr.emit_host(hs, mode))
 
     def _gen_algo(self, key: str):
@@ -165,7 +188,7 @@ def _bind(key: str):
     return temp_mem_size, inner, device, kernel, host, driver, function_call
 
 
-for _key in ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+for _key in ("joint_transforms", "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
              "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so",
              "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
     _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
@@ -189,7 +212,7 @@ GRiDCodeGenerator.gen_crba_device_temp_mem_size = GRiDCodeGenerator.gen_crba_inn
 # ----------------------------------------------------------------- file scaffolding
 from .emit import scaffold as _sc  # noqa: E402
 
-ALGO_ORDER = ("end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian",
+ALGO_ORDER = ("joint_transforms", "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian",
               "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
               "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so")
 
@@ -237,6 +260,15 @@ def gen_add_constants_helpers(self):
              "const int KNOTS_PER_WARP = 32;    // one lane owns one knot point",
              "const int SUGGESTED_THREADS = 32; // single-warp CTAs: warps never synchronise with each other"]
     per4, per8 = _scratch_constants(self)
+    ft = self.fixed_target_name
+    lines += [f"#define GRID_HAS_FIXED_TARGET {int(bool(ft))}", f'#define GRID_FIXED_TARGET_NAME "{ft}"']
+    if ft:   # un-suffixed aliases of the single-target EE launchers (the C ABI binds these)
+        lines += [f"#define GRID_FIXED_TARGET_POSE_LAUNCH end_effector_pose_{ft}_launch",
+                  f"#define GRID_FIXED_TARGET_GRADIENT_LAUNCH end_effector_pose_gradient_{ft}_launch",
+                  f"#define GRID_FIXED_TARGET_HESSIAN_LAUNCH end_effector_pose_gradient_hessian_{ft}_launch",
+                  f"#define GRID_FIXED_TARGET_POSE_CFG end_effector_pose_{ft}_cfg",
+                  f"#define GRID_FIXED_TARGET_GRADIENT_CFG end_effector_pose_gradient_{ft}_cfg",
+                  f"#define GRID_FIXED_TARGET_HESSIAN_CFG end_effector_pose_gradient_hessian_{ft}_cfg"]
     lines += [f"#define GRID_HAS_SECOND_ORDER {int(_hdr.second_order_enabled(self.max_tree))}",
               f"#define GRID_HAS_EE_HESSIAN {int(_hdr.ee_hessian_enabled(n))}",
               f"const size_t GRID_SCRATCH_ELEMS_PER_BLOCK_F32 = {per4};",
@@ -266,7 +298,11 @@ def gen_init_close_grid(self):
 
 def gen_all_code(self, use_thread_group=False, include_base_inertia=False, include_homogenous_transforms=False,
                  fixed_target_name=None, output_dir="."):
-    """Emit <namespace>.cuh into output_dir (reference GRiDCodeGenerator.py:309-437 writes it to the CWD)."""
+    """Emit <namespace>.cuh into output_dir (reference GRiDCodeGenerator.py:309-437 writes it to the CWD).
+    fixed_target_name: additionally generate the EE functions of that fixed joint (reference :310, :417)."""
+    if fixed_target_name is not None and (fixed_target_name or "") != self.fixed_target_name:
+        self._set_fixed_target(fixed_target_name or "")
+        self._bodies, self._sbodies = {}, {}
     self.code_str = ""
     self.indent_level = 0
     notes = ["Interface (same names as the reference GRiD header):",

@@ -419,7 +419,7 @@ __device__ __forceinline__ void tile_loop(const TileArgs<T>& a, unsigned char* s
 template <class A, typename T, bool OUT_STAGED>
 constexpr size_t split_smem_bytes() {
     size_t b = align16(size_t(A::SLOTS) * TILE * sizeof(T));
-    for (int s = 0; s < MAX_STREAMS; s++) b += 2 * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+    for (int s = 0; s < MAX_STREAMS; s++) b += A::NBUF * align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
     if (OUT_STAGED) b += align16(size_t(TILE) * A::OUT * sizeof(T));
     return b + 32;
 }
@@ -441,8 +441,8 @@ __device__ __forceinline__ void tile_loop_split(const TileArgs<T>& a, unsigned c
     for (int s = 0; s < MAX_STREAMS; s++)
 #pragma unroll
         for (int b = 0; b < 2; b++) {
-            in_off[s][b] = off;
-            off += align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
+            in_off[s][b] = (b < A::NBUF) ? off : in_off[s][0];
+            if (b < A::NBUF) off += align16(size_t(TILE) * in_n<A>(s) * sizeof(T));
         }
     const size_t stage_end = off;
     T* out_s = reinterpret_cast<T*>(smem + off);
@@ -490,11 +490,14 @@ __device__ __forceinline__ void tile_loop_split(const TileArgs<T>& a, unsigned c
     int buf = 0;
     if (tid == 0 && tile_is_tma(first)) issue_load(first, 0);
 
-    for (int tile = first; tile < num_tiles; tile += gridDim.x, buf ^= 1) {
+    // A::NBUF input buffers: 2 = the next tile's load is issued at the top of this tile (overlaps phase A and B);
+    // 1 = it is issued once phase A has consumed this tile's inputs (overlaps phase B only) -- chosen by the emitter
+    // when the second buffer would cost a resident CTA per SM.
+    for (int tile = first; tile < num_tiles; tile += gridDim.x, buf = (A::NBUF == 2) ? (buf ^ 1) : 0) {
         const int next = tile + gridDim.x;
         const bool tma = tile_is_tma(tile);
         const int nvalid = min(TILE, a.num_knots - tile * TILE);
-        if (tid == 0 && tile_is_tma(next)) issue_load(next, buf ^ 1);   // buf^1 was last read two barriers ago
+        if (A::NBUF == 2 && tid == 0 && tile_is_tma(next)) issue_load(next, buf ^ 1);   // buf^1 was last read two barriers ago
         if (A::PHASE_A_WRITES && OUT_STAGED) {                // phase A writes output rows too (side outputs)
             if (tid == 0) bulk_wait_read0();
             __syncthreads();
@@ -515,11 +518,13 @@ __device__ __forceinline__ void tile_loop_split(const TileArgs<T>& a, unsigned c
                     x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
             }
             A::template phaseA<TILE, 1>(warp, o, x[0], x[1], x[2], S, a.gravity);
+            if (A::NBUF == 1) fence_proxy_async();            // generic reads of the input buffer before its next TMA write
         }
         if (tma) phase[buf] ^= 1u;
         // the output rows may still be read by the previous tile's bulk store (issued by thread 0)
         if (OUT_STAGED && tid == 0) bulk_wait_read0();
         __syncthreads();                                      // state published, output rows free
+        if (A::NBUF == 1 && tid == 0 && tile_is_tma(next)) issue_load(next, 0);   // every phase-A warp is done with buffer 0
         A::template phaseB<TILE, 1>(warp, o, S);
         if (OUT_STAGED) {
             fence_proxy_async();

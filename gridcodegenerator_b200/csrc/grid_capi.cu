@@ -313,9 +313,10 @@ int grid_num_joints(void) { return N; }
 int grid_num_ees(void) { return grid::NUM_EES; }
 const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
 const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
-int grid_abi_version(void) { return 5; }
+int grid_abi_version(void) { return 6; }
 int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
 int grid_has_ee_hessian(void) { return GRID_HAS_EE_HESSIAN; }
+const char* grid_fixed_target_name(void) { return GRID_FIXED_TARGET_NAME; }
 long grid_kernel_info(int algo, int is_f64, int what) {
 #define DISPATCH(NAME) return is_f64 ? grid_capi_info_##NAME##_f64(algo, what) : grid_capi_info_##NAME##_f32(algo, what);
     switch (algo) {
@@ -603,6 +604,41 @@ int ee_hess_impl(const T* d_q, int stride, T* d_grad, T* d_hess, int nk, void* s
 #endif
 }
 template <typename T>
+int joint_transforms_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_joint_transforms", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)), grid::joint_transforms_cfg<T>::NEEDS_SCRATCH);
+    return fail(grid::joint_transforms_launch<T>(d_out, d_q, stride, m, nk, st), fn);
+}
+#if GRID_HAS_FIXED_TARGET
+template <typename T>
+int fixed_pose_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_fixed_target_pose", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)), grid::GRID_FIXED_TARGET_POSE_CFG<T>::NEEDS_SCRATCH);
+    return fail(grid::GRID_FIXED_TARGET_POSE_LAUNCH<T>(d_out, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+int fixed_grad_impl(const T* d_q, int stride, T* d_out, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_fixed_target_pose_gradient", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_out)), grid::GRID_FIXED_TARGET_GRADIENT_CFG<T>::NEEDS_SCRATCH);
+    return fail(grid::GRID_FIXED_TARGET_GRADIENT_LAUNCH<T>(d_out, d_q, stride, m, nk, st), fn);
+}
+template <typename T>
+int fixed_hess_impl(const T* d_q, int stride, T* d_grad, T* d_hess, int nk, void* s) {
+    GRID_CHECK_ARGS("grid_fixed_target_pose_gradient_hessian", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_hess)),
+                    grid::GRID_FIXED_TARGET_GRADIENT_CFG<T>::NEEDS_SCRATCH || grid::GRID_FIXED_TARGET_HESSIAN_CFG<T>::NEEDS_SCRATCH);
+    if (d_grad) {
+        cudaError_t e = grid::GRID_FIXED_TARGET_GRADIENT_LAUNCH<T>(d_grad, d_q, stride, m, nk, st);
+        if (e != cudaSuccess) return fail(e, fn);
+    }
+    return fail(grid::GRID_FIXED_TARGET_HESSIAN_LAUNCH<T>(d_hess, d_q, stride, m, nk, st), fn);
+}
+#else
+inline int no_fixed_target(const char* fn) {
+    grid_capi_last_error() = std::string(fn) + ": this library was built without a fixed kinematic target";
+    return static_cast<int>(cudaErrorNotSupported);
+}
+template <typename T> int fixed_pose_impl(const T*, int, T*, int, void*) { return no_fixed_target("grid_fixed_target_pose"); }
+template <typename T> int fixed_grad_impl(const T*, int, T*, int, void*) { return no_fixed_target("grid_fixed_target_pose_gradient"); }
+template <typename T> int fixed_hess_impl(const T*, int, T*, T*, int, void*) { return no_fixed_target("grid_fixed_target_pose_gradient_hessian"); }
+#endif
+template <typename T>
 long info_ee(int algo, int what) {
     using namespace grid;
     using RM = const robotModel<T>*;
@@ -622,6 +658,11 @@ long info_ee(int algo, int what) {
     extern "C" int grid_end_effector_pose_##SUF(const T* a, int st, T* o, int nk, void* s) { return ee_pose_impl<T>(a, st, o, nk, s); } \
     extern "C" int grid_end_effector_pose_gradient_##SUF(const T* a, int st, T* o, int nk, void* s) { return ee_grad_impl<T>(a, st, o, nk, s); } \
     extern "C" int grid_end_effector_pose_gradient_hessian_##SUF(const T* a, int st, T* g, T* h, int nk, void* s) { \
-        return ee_hess_impl<T>(a, st, g, h, nk, s); }
+        return ee_hess_impl<T>(a, st, g, h, nk, s); }                                                              \
+    extern "C" int grid_joint_transforms_##SUF(const T* a, int st, T* o, int nk, void* s) { return joint_transforms_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_fixed_target_pose_##SUF(const T* a, int st, T* o, int nk, void* s) { return fixed_pose_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_fixed_target_pose_gradient_##SUF(const T* a, int st, T* o, int nk, void* s) { return fixed_grad_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_fixed_target_pose_gradient_hessian_##SUF(const T* a, int st, T* g, T* h, int nk, void* s) { \
+        return fixed_hess_impl<T>(a, st, g, h, nk, s); }
 GRID_FOR_DTYPES(X_EE)
 #endif

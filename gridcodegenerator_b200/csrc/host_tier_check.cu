@@ -103,6 +103,10 @@ int main(int argc, char** argv) {
         section(hd_data->h_c, size_t(N) * n);    // 14 == 0
     }
 
+    // 15: cumulative joint transforms (the quantity the reference's X_single_thread / X_warp accumulate)
+    joint_transforms<T, true>(hd_data, d_robotModel, N, dimms, dimms, streams);
+    section(hd_data->h_jointXforms, size_t(N) * 16 * n);
+
     close_grid<T>(streams, d_robotModel, hd_data);
 
     f = fopen(argv[2], "wb");

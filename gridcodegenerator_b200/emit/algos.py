@@ -127,7 +127,8 @@ class Pusher:
 
 
 # ====================================================================== RNEA
-def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f", joints=None):
+def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f", joints=None,
+                 keep_Iv: bool = True):
     """v, a, f per joint in id order (ids are topologically sorted).  f_j -> state `fname`; with `keep`
     also v_j, I v_j and X a_parent (needed by the gradient).  `joints`: restrict to the joints of some base-rooted
     trees (they do not interact with the rest of a fixed-base robot)."""
@@ -164,7 +165,8 @@ def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: boo
         em.store_vec(fname, j, f)
         if keep:
             em.store_vec("v", j, v)
-            em.store_vec("Iv", j, Iv)
+            if keep_Iv:
+                em.store_vec("Iv", j, Iv)
             em.store_vec("Xa", j, aJ)
             if j in nonadj_parent:
                 em.store_vec("a", j, a)
@@ -411,7 +413,7 @@ def rnea_grad_columns(cx: Ctx, qd: Sequence[V], sink, cols: Optional[Sequence[in
             if j != c:
                 em.comment(f"grad RNEA column {c}, forward joint {j}")
             v = em.load_vec("v", j)
-            Iv = em.load_vec("Iv", j)
+            Iv = em.load_vec("Iv", j) if getattr(cx, "has_Iv", True) else inertia_mul(em, jd.I, v)
             if j == c:
                 Xa = em.load_vec("Xa", j)
                 dvq = mxS(em, S, v) if jd.parent >= 0 else [ZERO] * 6     # MxXv == Mxv since S x S = 0
@@ -1263,13 +1265,11 @@ def body_fdsva_so(model: Model) -> Body:
 
 
 # ================================================================= EE pose
-def ee_poses(cx: Ctx, order: int):
-    """Pose [x y z roll pitch yaw] of every leaf link frame in the base frame (reference
-    algorithms/_eepose_gradient_hessian.py:31-160): product of the homogeneous joint transforms down each chain,
-    then roll = atan2(R21, R22), pitch = -atan2(R20, sqrt(R21^2 + R22^2)), yaw = atan2(R10, R00) (:150-157).
-    With order 1 / 2 the pose entries carry their gradient / Hessian with respect to q (seed k = joint k); the
-    reference derives those by hand from dXhom / d2Xhom (:511-538, :985-1058), here they are the emit-time
-    tangents of the same chain product."""
+def hom_chain(cx: Ctx, order: int, before_joint=None, after_joint=None) -> Dict[int, List[List[V]]]:
+    """Tc[j] = rows 0..2 of the homogeneous transform base <- frame of joint j: the product of the joint transforms
+    Xhom(q) down the chain, following the parent topology (reference algorithms/_eepose_gradient_hessian.py:76-140
+    chains them leaf to root; :1226-1298 X_single_thread accumulates them root to leaf for serial chains).  With
+    order 1 / 2 the entries carry their gradient / Hessian with respect to q (seed k = joint k)."""
     from .spatial import hom_tables
     em, m, n = cx.em, cx.m, cx.n
     save = em.ad_order
@@ -1292,6 +1292,8 @@ def ee_poses(cx: Ctx, order: int):
                 e.append((float(Hq[r, c]), qv))
             return e
         p = m.parent[j]
+        if before_joint is not None:
+            before_joint(j)
         T = [[None] * 4 for _ in range(3)]
         for r in range(3):
             for c in range(4):
@@ -1304,50 +1306,146 @@ def ee_poses(cx: Ctx, order: int):
                             terms.append((coef, f, Tc[p][r][k]))
                     T[r][c] = em.lincomb(terms, Tc[p][r][3] if c == 3 else None)
         Tc[j] = T
-    poses = []
-    for e_ in m.robot.get_leaf_nodes():
-        T = Tc[e_]
-        roll = em.atan2(T[2][1], T[2][2])
-        sq = em.sqrt(em.lincomb([(1.0, T[2][1], T[2][1]), (1.0, T[2][2], T[2][2])]))
-        pitch = em.neg(em.atan2(T[2][0], sq))
-        yaw = em.atan2(T[1][0], T[0][0])
-        poses.append([T[0][3], T[1][3], T[2][3], roll, pitch, yaw])
+        if after_joint is not None:
+            local = [[em.lincomb([(coef, f) if f is not None else (coef, ONE) for coef, f in ent(r, c)])
+                      for c in range(4)] for r in range(3)]
+            after_joint(j, local, T)
     em.ad_order = save
-    return poses
+    return Tc
 
 
-def body_end_effector_pose(model: Model) -> Body:
+def fixed_target_transform(cx: Ctx, Tc, fixed_name: str, order: int):
+    """Transform base <- frame of the fixed joint `fixed_name` (a fixed kinematic target, reference
+    algorithms/_eepose_gradient_hessian.py:31-38, :89-93): chain of its parent body times its constant transform."""
+    em, m = cx.em, cx.m
+    fj = m.robot.get_fixed_joint_by_name(fixed_name)
+    import numpy as np
+    Xf = np.array(fj.Xhom_sympy().evalf(30), dtype=np.float64).reshape(4, 4)
+    Xf[np.abs(Xf) < 1e-12] = 0.0
+    p = fj.parent_joint_id
+    save = em.ad_order
+    em.ad_order = order
+    T = [[None] * 4 for _ in range(3)]
+    for r in range(3):
+        for c in range(4):
+            if p < 0:
+                T[r][c] = const(Xf[r, c])
+            else:
+                terms = [(float(Xf[k, c]), Tc[p][r][k]) for k in range(3) if Xf[k, c] != 0.0]
+                T[r][c] = em.lincomb(terms, Tc[p][r][3] if c == 3 else None)
+    em.ad_order = save
+    return T
+
+
+def pose_from_transform(cx: Ctx, T, order: int) -> List[V]:
+    """[x y z roll pitch yaw]: roll = atan2(R21, R22), pitch = -atan2(R20, sqrt(R21^2 + R22^2)), yaw = atan2(R10, R00)
+    (reference algorithms/_eepose_gradient_hessian.py:150-157)."""
+    em = cx.em
+    save = em.ad_order
+    em.ad_order = order
+    roll = em.atan2(T[2][1], T[2][2])
+    sq = em.sqrt(em.lincomb([(1.0, T[2][1], T[2][1]), (1.0, T[2][2], T[2][2])]))
+    pitch = em.neg(em.atan2(T[2][0], sq))
+    yaw = em.atan2(T[1][0], T[0][0])
+    em.ad_order = save
+    return [T[0][3], T[1][3], T[2][3], roll, pitch, yaw]
+
+
+def ee_poses(cx: Ctx, order: int, fixed_target: Optional[str] = None):
+    """Pose of every leaf link frame in the base frame (reference algorithms/_eepose_gradient_hessian.py:31-160), or of
+    ONE fixed kinematic target when `fixed_target` names a fixed joint (:34-37).  With order 1 / 2 the pose entries
+    carry their gradient / Hessian with respect to q; the reference derives those by hand from dXhom / d2Xhom
+    (:511-538, :985-1058), here they are the emit-time tangents of the same chain product."""
+    Tc = hom_chain(cx, order)
+    if fixed_target:
+        return [pose_from_transform(cx, fixed_target_transform(cx, Tc, fixed_target, order), order)]
+    return [pose_from_transform(cx, Tc[e_], order) for e_ in cx.m.robot.get_leaf_nodes()]
+
+
+def body_end_effector_pose(model: Model, fixed_target: Optional[str] = None) -> Body:
     """out[6*ee + o], o in x y z roll pitch yaw (reference :142-159)."""
     cx = _second_order_ctx(model)
-    for e_, pose in enumerate(ee_poses(cx, 0)):
+    for e_, pose in enumerate(ee_poses(cx, 0, fixed_target)):
         for o, v in enumerate(pose):
             _out(cx.em, 6 * e_ + o, v)
     return Body("end_effector_pose_inner", "", cx, "end-effector poses")
 
 
-def body_end_effector_pose_gradient(model: Model) -> Body:
+def body_end_effector_pose_gradient(model: Model, fixed_target: Optional[str] = None) -> Body:
     """out[(ee*n + j)*6 + o] = d pose_o / d q_j (reference s_deePos[6*deeInd + outputInd], :517-535)."""
     cx = _second_order_ctx(model)
     n = model.n
-    for e_, pose in enumerate(ee_poses(cx, 1)):
+    for e_, pose in enumerate(ee_poses(cx, 1, fixed_target)):
         for j in range(n):
             for o, v in enumerate(pose):
                 _out(cx.em, (e_ * n + j) * 6 + o, _d1(v, j))
     return Body("end_effector_pose_gradient_inner", "", cx, "gradient of the end-effector poses")
 
 
-def body_end_effector_pose_gradient_hessian(model: Model) -> Body:
+def body_end_effector_pose_gradient_hessian(model: Model, fixed_target: Optional[str] = None) -> Body:
     """Hessian[(ee*6 + o)*n*n + i*n + j] = d2 pose_o / dq_i dq_j (reference s_d2eePos[outputInd*n*n + i*n + j],
     :1024, :1056).  The gradient half of the reference kernel's two outputs (:1108) comes from the gradient kernel:
-    the host tier / C ABI launch both."""
+    the host tier / C ABI launch both.  An end effector depends only on the joints of its own chain, so for big
+    branched robots most of the 6 EE n^2 entries are structural zeros (Atlas: 27 000 outputs, 5 % non-zero): those
+    are written by one zero-fill loop instead of one store statement each."""
     cx = _second_order_ctx(model)
-    n = model.n
-    for e_, pose in enumerate(ee_poses(cx, 2)):
+    em, n = cx.em, model.n
+    poses = ee_poses(cx, 2, fixed_target)
+    entries = []
+    for e_, pose in enumerate(poses):
         for o, v in enumerate(pose):
             for i in range(n):
                 for j in range(n):
-                    _out(cx.em, (e_ * 6 + o) * n * n + i * n + j, _d2(v, i, j))
+                    entries.append(((e_ * 6 + o) * n * n + i * n + j, _d2(v, i, j)))
+    zeros = sum(1 for _, v in entries if v.is_zero())
+    if len(entries) > 2048 and 2 * zeros > len(entries):
+        _acquire_out(em)
+        em.line(f"for (int z_ = 0; z_ < {len(entries)}; ++z_) o[z_*OS] = T(0);")
+        entries = [(idx, v) for idx, v in entries if not v.is_zero()]
+    for idx, v in entries:
+        _out(em, idx, v)
     return Body("end_effector_pose_gradient_hessian_inner", "", cx, "Hessian of the end-effector poses")
+
+
+def code_X_single_thread(model: Model) -> str:
+    """Statements of X_single_thread(s_jointXforms, s_XmatsHom, s_q, tid) (reference signature,
+    algorithms/_eepose_gradient_hessian.py:1226-1298): fills the local homogeneous transforms Xhom_j(q_j) and the
+    cumulative transforms base <- joint j for every joint id <= tid, 16 values each, column-major."""
+    cx = Ctx(model)
+    em = cx.em
+    em.regs_only, em.fences, em.no_sync = True, False, True
+    em._out_acquired = True              # a plain device function: no tile staging buffer to acquire
+    cx.prologue(q_ptr="s_q")
+
+    def before(j):
+        em.line(f"if (tid < {j}) return;")
+
+    def after(j, local, T):
+        for c in range(4):
+            for r in range(3):
+                _out(em, 16 * j + r + 4 * c, local[r][c], ptr="s_XmatsHom")
+                _out(em, 16 * j + r + 4 * c, T[r][c], ptr="s_jointXforms")
+            _out(em, 16 * j + 3 + 4 * c, ONE if c == 3 else ZERO, ptr="s_XmatsHom")
+            _out(em, 16 * j + 3 + 4 * c, ONE if c == 3 else ZERO, ptr="s_jointXforms")
+
+    hom_chain(cx, 0, before_joint=before, after_joint=after)
+    return em.code()
+
+
+def body_joint_transforms(model: Model) -> Body:
+    """Cumulative homogeneous transforms of every joint frame: out[16*j + r + 4*c] = (base <- joint j)[r][c],
+    column-major 4 x 4 blocks (what the reference's X_single_thread / X_warp leave in s_jointXforms,
+    algorithms/_eepose_gradient_hessian.py:1226-1398; those assume a serial chain, here the parent topology is
+    followed)."""
+    cx = _second_order_ctx(model)
+    em = cx.em
+    Tc = hom_chain(cx, 0)
+    for j in range(model.n):
+        for c in range(4):
+            for r in range(3):
+                _out(em, 16 * j + r + 4 * c, Tc[j][r][c])
+            _out(em, 16 * j + 3 + 4 * c, ONE if c == 3 else ZERO)
+    return Body("joint_transforms_inner", "", cx, "cumulative joint transforms (4 x 4, column-major, per joint)")
 
 
 # ============================================================ split (warp-specialised) bodies
@@ -1394,7 +1492,7 @@ def _publish_state(cx: Ctx, qd: Sequence[V], extra=(), joints=None):
     act = [j for j in range(n) if joints is None or j in joints]
     keys = []
     for j in act:
-        for nm in ("v", "Iv", "Xa", "f"):
+        for nm in (("v", "Iv", "Xa", "f") if getattr(cx, "has_Iv", True) else ("v", "Xa", "f")):
             keys += [(nm, j, k) for k in range(6)]
     keys += list(extra)
     pending = []
@@ -1422,6 +1520,7 @@ def _column_ctx(cx: Ctx, c: int) -> Ctx:
     emc = cx.em.fork()
     cc = Ctx.__new__(Ctx)
     cc.m, cc.em, cc.n, cc.gravity = m, emc, cx.n, cx.gravity
+    cc.has_Iv = getattr(cx, "has_Iv", True)
     touched = sorted(set(m.subtree[c]) | set(m.ancestors[c]))
     cc.X = [None] * m.n
     cc.trig = [None] * m.n
@@ -1455,6 +1554,17 @@ def split_phase_a_regs_policy(n: int) -> bool:
     return regs_only_policy(n)
 
 
+def split_publish_Iv_policy(n: int) -> bool:
+    """Publish I v per joint (6 n state slots) or let the column functions recompute it from v.  Big robots recompute:
+    Atlas' published state drops from 931 to 751 slots (119 -> 96 KB per 32-knot tile), which is what lets TWO CTAs
+    reside on an SM -- the split kernels of big robots are bound by per-warp instruction-fetch latency, so resident warps
+    are throughput -- for ~6 % more operations."""
+    mode = os.environ.get("GRID_SPLIT_PUBLISH_IV", "auto")
+    if mode in ("0", "1"):
+        return mode == "1"
+    return n <= 16          # HyQ (12 joints, 36 KB of state) keeps it: recomputing would cost 9 % for nothing
+
+
 def _split_columns(cx: Ctx, sink_factory):
     cols = []
     for c in range(cx.n):
@@ -1485,13 +1595,14 @@ def split_inverse_dynamics_gradient(model: Model, use_qdd: bool) -> SplitBody:
     cx = Ctx(model)
     em, n = cx.em, model.n
     em.no_sync = True
+    cx.has_Iv = split_publish_Iv_policy(n)
     parts = []
     for js in tree_parts(model):
         ops0 = _begin_part(cx)
         cx.prologue(joints=js)
         qd = cx.read_vec("qd", "qd_", js)
         qdd = cx.read_vec("qdd", "qdd_", js) if use_qdd else None
-        rnea_forward(cx, qd, qdd, keep=True, joints=js)
+        rnea_forward(cx, qd, qdd, keep=True, joints=js, keep_Iv=cx.has_Iv)
         rnea_backward(cx, qd, keep_f=True, joints=js)
         _publish_state(cx, qd, joints=js)
         parts.append((em.code(), em.n_ops - ops0))
@@ -1515,6 +1626,7 @@ def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -
     cx = Ctx(model)
     em, n = cx.em, model.n
     em.no_sync = True
+    cx.has_Iv = split_publish_Iv_policy(n)
     parts = []
     L_all: Dict[tuple, V] = {}
     for js in tree_parts(model):
@@ -1549,7 +1661,7 @@ def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -
             for j in act:
                 _out(em, 3 * n * n + j, qdd[j])
         em.comment("---- pass 2: RNEA(q, qd, qdd) keeping v, Iv, X a_parent, f")
-        rnea_forward(cx, qd, qdd, keep=True, joints=js)
+        rnea_forward(cx, qd, qdd, keep=True, joints=js, keep_Iv=cx.has_Iv)
         rnea_backward(cx, qd, keep_f=True, joints=js)
         lkeys = [("L",) + k_ for k_ in L] + [("Dinv2", i_, 0) for i_ in act]
         _publish_state(cx, qd, extra=lkeys, joints=js)

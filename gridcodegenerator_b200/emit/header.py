@@ -35,13 +35,38 @@ class AlgoSpec:
     out_n: Callable[[int], int]
     uses_gravity: bool = True
     extra_kernel_params: str = ""
+    fixed_target: str = ""   # name of the fixed joint this (single-target EE) variant is about
 
 
-def specs(n: int, num_ees: int = 1, max_tree: Optional[int] = None) -> List[AlgoSpec]:
-    """max_tree: joints of the largest base-rooted tree of the robot (default n: one tree)."""
+def fixed_target_specs(n: int, name: str) -> List[AlgoSpec]:
+    """EE pose / gradient / Hessian of ONE fixed kinematic target (reference gen_all_code(fixed_target_name=...),
+    GRiDCodeGenerator.py:309-310, :417; function names carry the target's name as a suffix like the reference's,
+    algorithms/_eepose_gradient_hessian.py:46, :176, :207, :264)."""
+    out = [
+        AlgoSpec("end_effector_pose", f"end_effector_pose_{name}", "EE_FIXED", "",
+                 lambda m: algos.body_end_effector_pose(m, name),
+                 ["q"], [("d_q", n)], [(0, 0)], "d_eePos", lambda n: 6, uses_gravity=False),
+        AlgoSpec("end_effector_pose_gradient", f"end_effector_pose_gradient_{name}", "DEE_FIXED", "",
+                 lambda m: algos.body_end_effector_pose_gradient(m, name),
+                 ["q"], [("d_q", n)], [(0, 0)], "d_deePos", lambda n: 6 * n, uses_gravity=False),
+        AlgoSpec("end_effector_pose_gradient_hessian", f"end_effector_pose_gradient_hessian_{name}", "D2EE_FIXED", "",
+                 lambda m: algos.body_end_effector_pose_gradient_hessian(m, name),
+                 ["q"], [("d_q", n)], [(0, 0)], "d_d2eePos", lambda n: 6 * n * n, uses_gravity=False),
+    ]
+    for sp in out:
+        sp.fixed_target = name
+    return out
+
+
+def specs(n: int, num_ees: int = 1, max_tree: Optional[int] = None, fixed_target: Optional[str] = None) -> List[AlgoSpec]:
+    """max_tree: joints of the largest base-rooted tree of the robot (default n: one tree).
+    fixed_target: name of a fixed joint for which the additional single-target EE functions are generated."""
     ee = num_ees
     max_tree = n if max_tree is None else max_tree
-    return [
+    return (fixed_target_specs(n, fixed_target) if fixed_target else []) + [
+        AlgoSpec("joint_transforms", "joint_transforms", "JX", "", algos.body_joint_transforms,
+                 ["q"], [("d_q", n)], [(0, 0)], "d_jointXforms", lambda n: 16 * n, uses_gravity=False),
+    ] + [
         AlgoSpec("end_effector_pose", "end_effector_pose", "EE", "", algos.body_end_effector_pose,
                  ["q"], [("d_q", n)], [(0, 0)], "d_eePos", lambda n: 6 * ee, uses_gravity=False),
         AlgoSpec("end_effector_pose_gradient", "end_effector_pose_gradient", "DEE", "",
@@ -94,9 +119,10 @@ def specs(n: int, num_ees: int = 1, max_tree: Optional[int] = None) -> List[Algo
 
 
 def ee_hessian_enabled(n: int) -> bool:
-    """The EE Hessian has 6 EE n^2 outputs per knot (27 000 for Atlas); it is generated for robots up to
-    GRID_EE_HESSIAN_MAX_JOINTS joints (default 16: iiwa14, HyQ), the pose and its gradient for every robot."""
-    return n <= int(os.environ.get("GRID_EE_HESSIAN_MAX_JOINTS", "16"))
+    """The EE Hessian has 6 EE n^2 outputs per knot (27 000 for Atlas, 95 % of them structural zeros); it is generated
+    for robots up to GRID_EE_HESSIAN_MAX_JOINTS joints (default 64), the pose and its gradient for every robot.  Outputs
+    that large go through plain per-lane stores (choose_config), not the transposed-store scratch."""
+    return n <= int(os.environ.get("GRID_EE_HESSIAN_MAX_JOINTS", "64"))
 
 
 def second_order_enabled(max_tree: int) -> bool:
@@ -129,6 +155,11 @@ def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     fit = (SMEM_LIMIT - 16) // (state_w + 32 * 33 * sizeof)
     if best is not None and (best[0] >= 4 or fit < 2 * best[0] or os.environ.get("GRID_NO_TRANSPOSED") == "1"):
         return 32 * best[0], True, best[1]
+    # Outputs beyond 1 MB per warp tile (Atlas EE Hessian: 27 000 values per knot) would need gigabytes of
+    # transposed-store scratch per in-flight launch: each lane stores straight into its own output row instead.
+    if 32 * out_elems * sizeof > (1 << 20):
+        fit_state = max(1, (SMEM_LIMIT - 16) // max(state_w, 1))
+        return 32 * min(MAX_WARPS, fit_state), True, 0
     # Staging a large per-knot output (Atlas matrices, second-order tensors) in shared memory would leave 1-3 warps
     # per SM.  STAGED = 3: every lane writes its output row into a lane-interleaved global scratch (element idx at
     # [idx*32 + lane]: each store instruction is one full 128-byte line), then the CTA transposes the scratch into
@@ -228,18 +259,46 @@ def split_assign(sb: "algos.SplitBody", max_warps: int = 0):
     return [sorted(g) for g in best if g]
 
 
-def split_maxnreg(nw: int) -> int:
-    """Largest register budget per thread that lets one CTA of nw warps launch: each of the SM's four schedulers
-    owns 16384 registers and hosts ceil(nw / 4) of the CTA's warps."""
-    per_sched = -(-nw // 4)
-    return min(255, (16384 // (per_sched * 32)) // 8 * 8)
+def split_maxnreg(nw: int, ctas: int = 1) -> int:
+    """Largest register budget per thread that lets `ctas` CTAs of nw warps reside on an SM: each of the SM's four
+    schedulers owns 16384 registers and hosts ceil(nw / 4) warps of every CTA."""
+    per_sched = ctas * -(-nw // 4)
+    return max(32, min(255, (16384 // (per_sched * 32)) // 8 * 8))
+
+
+SMEM_PER_SM = 232448            # 227 KB; every resident CTA also reserves 1 KB
+
+
+def split_smem_plan(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int):
+    """(OUT_STAGED, NBUF, resident CTAs per SM that shared memory allows, bytes) for the split form.
+    Output rows are staged in shared memory (one TMA bulk store per tile) when that fits at all.  Inputs are double
+    buffered unless dropping the second buffer buys a second resident CTA: the split kernels of big robots are bound
+    by per-warp instruction-fetch latency (Atlas: every warp streams its own ~100 KB of straight-line code), so a
+    second CTA per SM is worth far more than overlapping a 12 KB load with phase A."""
+    a16 = lambda x: (x + 15) & ~15
+    state = a16(max(sb.nslots, 1) * 32 * sizeof)
+    ins = sum(a16(32 * e * sizeof) for _, e in sp.streams)
+    out = a16(32 * sp.out_n(n) * sizeof)
+    half = (SMEM_PER_SM - 2 * 1024) // 2
+    forced = os.environ.get("GRID_SPLIT_NBUF", "")
+    best = None
+    for staged in (True, False):
+        for nbuf in ([int(forced)] if forced else (2, 1)):
+            need = state + nbuf * ins + (out if staged else 0) + 32
+            if need > SMEM_LIMIT:
+                continue
+            ctas = 2 if need <= half else 1
+            cand = (staged, nbuf, ctas, need)
+            # preference: staged output first; then two resident CTAs; then double buffering
+            if best is None or (cand[0], cand[2], cand[1]) > (best[0], best[2], best[1]):
+                best = cand
+        if best is not None and best[0]:
+            break
+    return best or (False, 1, 1, state + ins + 32)
 
 
 def split_out_staged(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> bool:
-    a16 = lambda x: (x + 15) & ~15
-    need = a16(max(sb.nslots, 1) * 32 * sizeof) + sum(2 * a16(32 * e * sizeof) for _, e in sp.streams) \
-        + a16(32 * sp.out_n(n) * sizeof) + 32
-    return need <= SMEM_LIMIT
+    return split_smem_plan(sb, sp, n, sizeof)[0]
 
 
 def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1) -> str:
@@ -263,6 +322,8 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     groups = split_assign(sb)
     na = len(sb.parts)
     nw = max(len(groups), na)
+    plan4 = split_smem_plan(sb, sp, n, 4)
+    plan8 = split_smem_plan(sb, sp, n, 8)
     IN = [e for _, e in sp.streams] + [0, 0, 0]
     args = []
     for (s_, off) in sp.split:
@@ -278,6 +339,7 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
                f"    static constexpr int SLOTS = {max(sb.nslots, 1)};\n"
                f"    static constexpr int NW = {nw};          // warps per CTA = column groups of phase B\n"
                f"    static constexpr int NA = {na};           // warps running phase A (one part each)\n"
+               f"    static constexpr int NBUF = sizeof(T) == 4 ? {plan4[1]} : {plan8[1]};   // input staging buffers\n"
                f"    static constexpr bool PHASE_A_WRITES = {'true' if writes else 'false'};\n"
                f"    template <int NT, int OS>\n"
                f"    static __device__ __forceinline__ void phaseA(int warp, T* __restrict__ o, const T* __restrict__ x0, "
@@ -288,8 +350,7 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
                f"    template <int NT, int OS>\n"
                f"    static __device__ __forceinline__ void phaseB(int warp, T* __restrict__ o, T* __restrict__ S) {{\n"
                f"        switch (warp) {{\n" + "\n".join(cases) + "\n            default: break;\n        }\n    }\n};\n\n")
-    st4 = split_out_staged(sb, sp, n, 4)
-    st8 = split_out_staged(sb, sp, n, 8)
+    st4, st8 = plan4[0], plan8[0]
     b = lambda x: "true" if x else "false"
     A = f"{stem}_algo"
     regs = int(os.environ.get("GRID_SPLIT_MAXNREG", "0"))
@@ -308,7 +369,10 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
         fill.append(f"    a.in[{i}] = nullptr; a.stride[{i}] = 0;")
     gv = "gravity" if sp.uses_gravity else "T(0)"
     C = f"{stem}_cfg<T>"
-    bounds = f"__maxnreg__({regs or split_maxnreg(nw)})"
+    # register budget for as many resident CTAs as the fp32 shared-memory plan allows (at most two)
+    # (only when that leaves >= 128 registers per thread: HyQ's 12-warp CTAs keep the whole register file)
+    two = split_maxnreg(nw, 2) if plan4[2] >= 2 else 0
+    bounds = f"__maxnreg__({regs or (two if two >= 128 else split_maxnreg(nw, 1))})"
     out.append(f"template <typename T>\n__global__ void {bounds}\n"
                f"{sp.fn}_split_kernel({kernel_params(sp)}) {{\n"
                f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"
@@ -450,7 +514,7 @@ def _sig_types(sp: AlgoSpec) -> str:
 # ------------------------------------------------------------------ host tier
 @dataclass
 class HostSpec:
-    fn: str
+    fn: str                         # C++ function stem; for fixed-target EE variants it carries the target suffix
     tmpl: str                       # template parameter list after "typename T"
     label: str                      # name printed by _single_timing
     uses_gravity: bool
@@ -459,16 +523,41 @@ class HostSpec:
     launch: List[str]               # lines performing the launch into `err`
     d2h: Tuple[str, str, str]       # (d_ptr, h_ptr, elements per knot)
     extra_d2h: List[Tuple[str, str, str]] = field(default_factory=list)
+    key: str = ""                   # generator key (gen_<key>_host); defaults to fn
 
 
-def host_specs(n: int) -> List[HostSpec]:
+def host_specs(n: int, fixed_target: str = "") -> List[HostSpec]:
     qsel = ["const int stride_q = USE_COMPRESSED_MEM ? NUM_JOINTS : 3*NUM_JOINTS;",
             "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q : hd_data->d_q_qd_u;",
             "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q : hd_data->h_q_qd_u;"]
     comp = ["const int stride_q_qd = USE_COMPRESSED_MEM ? 2*NUM_JOINTS : 3*NUM_JOINTS;",
             "T *d_in = USE_COMPRESSED_MEM ? hd_data->d_q_qd : hd_data->d_q_qd_u;",
             "T *h_in = USE_COMPRESSED_MEM ? hd_data->h_q_qd : hd_data->h_q_qd_u;"]
-    return [
+    ft = []
+    if fixed_target:
+        sfx = "_" + fixed_target
+        ft = [
+            HostSpec("end_effector_pose" + sfx, ", bool USE_COMPRESSED_MEM = false", "EE_POS", False, qsel,
+                     [("", "d_in", "h_in", "stride_q")],
+                     [f"err = end_effector_pose{sfx}_launch<T>(hd_data->d_eePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                     ("hd_data->d_eePos", "hd_data->h_eePos", "6"), key="end_effector_pose"),
+            HostSpec("end_effector_pose_gradient" + sfx, ", bool USE_COMPRESSED_MEM = false", "DEE_POS", False, qsel,
+                     [("", "d_in", "h_in", "stride_q")],
+                     [f"err = end_effector_pose_gradient{sfx}_launch<T>(hd_data->d_deePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                     ("hd_data->d_deePos", "hd_data->h_deePos", "6*NUM_JOINTS"), key="end_effector_pose_gradient"),
+            HostSpec("end_effector_pose_gradient_hessian" + sfx, ", bool USE_COMPRESSED_MEM = false", "D2EE_POS", False, qsel,
+                     [("", "d_in", "h_in", "stride_q")],
+                     [f"err = end_effector_pose_gradient{sfx}_launch<T>(hd_data->d_deePos, d_in, stride_q, d_robotModel, num_timesteps, 0);",
+                      f"if (err == cudaSuccess) err = end_effector_pose_gradient_hessian{sfx}_launch<T>(hd_data->d_d2eePos, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                     ("hd_data->d_d2eePos", "hd_data->h_d2eePos", "6*NUM_JOINTS*NUM_JOINTS"),
+                     extra_d2h=[("hd_data->d_deePos", "hd_data->h_deePos", "6*NUM_JOINTS")],
+                     key="end_effector_pose_gradient_hessian"),
+        ]
+    return ft + [
+        HostSpec("joint_transforms", ", bool USE_COMPRESSED_MEM = false", "JOINT_XFORMS", False, qsel,
+                 [("", "d_in", "h_in", "stride_q")],
+                 ["err = joint_transforms_launch<T>(hd_data->d_jointXforms, d_in, stride_q, d_robotModel, num_timesteps, 0);"],
+                 ("hd_data->d_jointXforms", "hd_data->h_jointXforms", "16*NUM_JOINTS")),
         HostSpec("inverse_dynamics", ", bool USE_QDD_FLAG = false, bool USE_COMPRESSED_MEM = false", "ID", True, comp,
                  [("", "d_in", "h_in", "stride_q_qd"), ("USE_QDD_FLAG", "hd_data->d_qdd", "hd_data->h_qdd", "NUM_JOINTS")],
                  ["if (USE_QDD_FLAG) err = inverse_dynamics_qdd_launch<T>(hd_data->d_c, d_in, stride_q_qd, hd_data->d_qdd, d_robotModel, gravity, num_timesteps, 0);",

@@ -76,6 +76,7 @@ struct gridData {
     T *d_eePos;
     T *d_deePos;
     T *d_d2eePos;
+    T *d_jointXforms; // 16 n per knot: cumulative 4 x 4 joint transforms (joint_transforms)
     T *d_idsva_so;   // 4 n^3 per knot, allocated only when GRID_HAS_SECOND_ORDER
     T *d_df2;
     // CPU OUTPUTS (pinned)
@@ -89,6 +90,7 @@ struct gridData {
     T *h_eePos;
     T *h_deePos;
     T *h_d2eePos;
+    T *h_jointXforms;
     T *h_idsva_so;
     T *h_df2;
 };
@@ -151,6 +153,8 @@ gridData<T> *init_gridData(const int num_timesteps){
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_eePos, 6*NUM_EES*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_deePos, 6*NUM_EES*n*N*sizeof(T)));
     gpuErrchk(cudaMallocHost((void**)&hd_data->h_d2eePos, 6*NUM_EES*n*n*N*sizeof(T)));
+    gpuErrchk(cudaMalloc((void**)&hd_data->d_jointXforms, 16*n*N*sizeof(T)));
+    gpuErrchk(cudaMallocHost((void**)&hd_data->h_jointXforms, 16*n*N*sizeof(T)));
     hd_data->d_idsva_so = hd_data->d_df2 = hd_data->h_idsva_so = hd_data->h_df2 = nullptr;
 #if GRID_HAS_SECOND_ORDER
     gpuErrchk(cudaMalloc((void**)&hd_data->d_idsva_so, 4*n*n*n*N*sizeof(T)));
@@ -202,6 +206,7 @@ void close_grid(cudaStream_t *streams, robotModel<T> *d_robotModel, gridData<T> 
         gpuErrchk(cudaFreeHost(hd_data->h_M)); gpuErrchk(cudaFreeHost(hd_data->h_dc_du)); gpuErrchk(cudaFreeHost(hd_data->h_df_du));
         gpuErrchk(cudaFree(hd_data->d_eePos)); gpuErrchk(cudaFree(hd_data->d_deePos)); gpuErrchk(cudaFree(hd_data->d_d2eePos));
         gpuErrchk(cudaFreeHost(hd_data->h_eePos)); gpuErrchk(cudaFreeHost(hd_data->h_deePos)); gpuErrchk(cudaFreeHost(hd_data->h_d2eePos));
+        gpuErrchk(cudaFree(hd_data->d_jointXforms)); gpuErrchk(cudaFreeHost(hd_data->h_jointXforms));
         if (hd_data->d_idsva_so) { gpuErrchk(cudaFree(hd_data->d_idsva_so)); gpuErrchk(cudaFree(hd_data->d_df2)); }
         if (hd_data->h_idsva_so) { gpuErrchk(cudaFreeHost(hd_data->h_idsva_so)); gpuErrchk(cudaFreeHost(hd_data->h_df2)); }
         free(hd_data);

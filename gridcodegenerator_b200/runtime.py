@@ -123,7 +123,11 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
     name = robot.name
     out_dir = os.path.join(BUILD_DIR, name)
     os.makedirs(out_dir, exist_ok=True)
-    gen = GRiDCodeGenerator(robot)
+    # fixed kinematic target of the library's single-target EE entry points: the robot's first fixed joint, if any
+    ft = os.environ.get("GRID_FIXED_TARGET")
+    if ft is None:
+        ft = robot.fixed_joints[0].get_name() if getattr(robot, "fixed_joints", None) else ""
+    gen = GRiDCodeGenerator(robot, fixed_target_name=ft)
     gen.gen_all_code(output_dir=out_dir)
     digest = _source_digest(gen.code_str)
     pkg_digest = _package_digest()          # taken BEFORE compiling: edits made during a long build must not be stamped
@@ -235,6 +239,12 @@ class GRiDLibrary:
             getattr(L, f"grid_end_effector_pose_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_end_effector_pose_gradient_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_end_effector_pose_gradient_hessian_{suf}").argtypes = [vp, ci, vp, vp, ci, vp]
+            getattr(L, f"grid_joint_transforms_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_fixed_target_pose_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_fixed_target_pose_gradient_{suf}").argtypes = [vp, ci, vp, ci, vp]
+            getattr(L, f"grid_fixed_target_pose_gradient_hessian_{suf}").argtypes = [vp, ci, vp, vp, ci, vp]
+        L.grid_fixed_target_name.restype = ctypes.c_char_p
+        self.fixed_target = L.grid_fixed_target_name().decode()
         self.has_second_order = bool(L.grid_has_second_order())
         self.has_ee_hessian = bool(L.grid_has_ee_hessian())
         self.num_ees = int(L.grid_num_ees())
@@ -435,6 +445,36 @@ class GRiDLibrary:
         h = torch.empty((B, 6 * self.num_ees * n * n), dtype=q.dtype, device=q.device)
         with torch.cuda.device(q.device):
             self._check(getattr(self.lib, f"grid_end_effector_pose_gradient_hessian_{self._suf(q)}")(
+                p, stride, g.data_ptr(), h.data_ptr(), B, self._stream()))
+        return g, h
+
+    def joint_transforms(self, q, out=None):
+        """-> (B, 16 n): cumulative transform base <- joint j at [16 j + r + 4 c] (4 x 4 column-major per joint)."""
+        import torch
+        p, stride, B = self._dev(q, self.n)
+        out = self._out(out, q, B, 16 * self.n)
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_joint_transforms_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
+        return out
+
+    def fixed_target_pose(self, q, out=None):
+        """Pose [x y z roll pitch yaw] of the library's fixed kinematic target (self.fixed_target) -> (B, 6)."""
+        import torch
+        p, stride, B = self._dev(q, self.n)
+        out = self._out(out, q, B, 6)
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_fixed_target_pose_{self._suf(q)}")(p, stride, out.data_ptr(), B, self._stream()))
+        return out
+
+    def fixed_target_pose_gradient_hessian(self, q):
+        """-> (gradient (B, 6 n) at [j*6 + o], Hessian (B, 6 n^2) at [o*n*n + i*n + j]) of the fixed target's pose."""
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q, n)
+        g = torch.empty((B, 6 * n), dtype=q.dtype, device=q.device)
+        h = torch.empty((B, 6 * n * n), dtype=q.dtype, device=q.device)
+        with torch.cuda.device(q.device):
+            self._check(getattr(self.lib, f"grid_fixed_target_pose_gradient_hessian_{self._suf(q)}")(
                 p, stride, g.data_ptr(), h.data_ptr(), B, self._stream()))
         return g, h
 

@@ -151,6 +151,27 @@ int grid_inverse_dynamics_host_f32(const float *h_q_qd_u, float *h_c, int num_kn
 /* release the cached device workspace of the host entry points and the robot model handles */
 int grid_release(void);
 
+/* ---- cumulative joint transforms: out[16*j + r + 4*c] = (base <- frame of joint j)[r][c], 4 x 4 column-major per joint
+ * replaces what X_single_thread / X_warp leave in s_jointXforms (algorithms/_eepose_gradient_hessian.py:1226-1398; the
+ * emitted header also provides those two device functions with the reference's signatures). d_q: rows starting with q. */
+int grid_joint_transforms_f32(const float *d_q, int stride, float *d_jointXforms, int num_knots, void *stream);
+int grid_joint_transforms_f64(const double *d_q, int stride, double *d_jointXforms, int num_knots, void *stream);
+
+/* ---- end-effector functions of ONE fixed kinematic target (a fixed joint chosen when the library is generated)
+ * replaces end_effector_pose_<target> / _gradient_<target> / _gradient_hessian_<target> that the reference emits for
+ * gen_all_code(fixed_target_name=...) (GRiDCodeGenerator.py:309-310, :417; algorithms/_eepose_gradient_hessian.py:31-38).
+ * grid_fixed_target_name() is "" when the library has none (the calls then return cudaErrorNotSupported).
+ * pose: 6 per knot; gradient: out[j*6 + o]; Hessian: out[o*n*n + i*n + j]; d_grad may be NULL. */
+const char *grid_fixed_target_name(void);
+int grid_fixed_target_pose_f32(const float *d_q, int stride, float *d_pose, int num_knots, void *stream);
+int grid_fixed_target_pose_f64(const double *d_q, int stride, double *d_pose, int num_knots, void *stream);
+int grid_fixed_target_pose_gradient_f32(const float *d_q, int stride, float *d_grad, int num_knots, void *stream);
+int grid_fixed_target_pose_gradient_f64(const double *d_q, int stride, double *d_grad, int num_knots, void *stream);
+int grid_fixed_target_pose_gradient_hessian_f32(const float *d_q, int stride, float *d_grad, float *d_hess, int num_knots,
+                                                void *stream);
+int grid_fixed_target_pose_gradient_hessian_f64(const double *d_q, int stride, double *d_grad, double *d_hess, int num_knots,
+                                                void *stream);
+
 /* ---- grad FD without any allocation
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

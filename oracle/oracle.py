@@ -91,6 +91,9 @@ class Oracle:
         hs = [np.ascontiguousarray(np.stack([h[i] for h in H]), dtype=np.float64) for i in range(4)]
         leaves = np.ascontiguousarray(robot.get_leaf_nodes(), dtype=np.int32)
         self.nleaf = len(leaves)
+        self._hom = hs                                   # H0, Hs, Hc, Hq stacked per joint (numpy functions below)
+        self._parent = [int(p) for p in par]
+        self._robot = robot
         L.rbd_model_set_hom.argtypes = [ctypes.c_void_p, _dp, _dp, _dp, _dp, ctypes.c_int, _ip]
         L.rbd_model_set_hom(self._h, *[_d(a) for a in hs], ctypes.c_int(self.nleaf), leaves.ctypes.data_as(_ip))
 
@@ -199,3 +202,35 @@ class Oracle:
     def batch_ee_pose_hessian(self, x, nthreads=0):
         """out[(ee*6 + o)*n*n + i*n + j] (second central differences of the pose, ~1e-7 accurate)."""
         return self._batch(self.L.rbd_batch_ee_pose_hessian, x, 6 * self.nleaf * self.n ** 2, nthreads=nthreads)
+
+    # ------------------------------------------------- homogeneous chain (numpy; small and not timed)
+    def _chain(self, x):
+        """T[j]: (B, 4, 4) transform base <- frame of joint j: product of Xhom_j(q_j) down the parent chain
+        (reference algorithms/_eepose_gradient_hessian.py:76-140; X_single_thread :1226-1298 for serial chains)."""
+        x = _arr(x)
+        q = x[:, :self.n]
+        H0, Hs, Hc, Hq = self._hom
+        T = []
+        for j in range(self.n):
+            Xj = (H0[j][None] + np.sin(q[:, j])[:, None, None] * Hs[j][None] + np.cos(q[:, j])[:, None, None] * Hc[j][None]
+                  + q[:, j][:, None, None] * Hq[j][None])
+            p = self._parent[j]
+            T.append(Xj if p < 0 else np.einsum("bik,bkj->bij", T[p], Xj))
+        return T
+
+    def batch_joint_transforms(self, x):
+        """(B, >= n) rows starting with q -> (B, 16 n): out[16 j + r + 4 c] = (base <- joint j)[r][c]."""
+        T = self._chain(x)
+        return np.concatenate([t.transpose(0, 2, 1).reshape(len(t), 16) for t in T], axis=1)
+
+    def batch_fixed_target_pose(self, x, fixed_name):
+        """Pose [x y z roll pitch yaw] of the fixed joint `fixed_name` (reference :31-38, :89-93, :150-157) -> (B, 6)."""
+        fj = self._robot.get_fixed_joint_by_name(fixed_name)
+        Xf = np.array(fj.Xhom_sympy().evalf(30), dtype=np.float64).reshape(4, 4)
+        T = self._chain(x)
+        B = len(_arr(x))
+        M = np.broadcast_to(Xf, (B, 4, 4)) if fj.parent_joint_id < 0 else np.einsum("bik,kj->bij", T[fj.parent_joint_id], Xf)
+        roll = np.arctan2(M[:, 2, 1], M[:, 2, 2])
+        pitch = -np.arctan2(M[:, 2, 0], np.sqrt(M[:, 2, 1] ** 2 + M[:, 2, 2] ** 2))
+        yaw = np.arctan2(M[:, 1, 0], M[:, 0, 0])
+        return np.stack([M[:, 0, 3], M[:, 1, 3], M[:, 2, 3], roll, pitch, yaw], axis=1)

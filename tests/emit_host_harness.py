@@ -37,7 +37,8 @@ static inline double_pair pneg(double_pair a) { return mkp<double>(-a.x, -a.y); 
 
 
 def build_host_inners(robot, workdir=None, second_order=False):
-    g = GRiDCodeGenerator(robot)
+    ft = robot.fixed_joints[0].get_name() if getattr(robot, "fixed_joints", None) else ""
+    g = GRiDCodeGenerator(robot, fixed_target_name=ft)     # like runtime.build_library: first fixed joint as the target
     n = g.model.n
     src = [PRELUDE]
     wrappers = []
@@ -69,6 +70,12 @@ def build_host_inners(robot, workdir=None, second_order=False):
                 f"    static thread_local double S[{max(sb.nslots, 1)}];\n"
                 + "".join(f"    {stem}_phaseA{p_}<double, 1>(o, {call}, S, gravity);\n" for p_ in range(len(sb.parts)))
                 + f"{cols}}}\n")
+    # the reference-signature helper X_single_thread (algorithms/_eepose_gradient_hessian.py:1226-1298)
+    from gridcodegenerator_b200.emit import algos as _algos
+    src.append("template <typename T>\nvoid X_single_thread(T *s_jointXforms, T *s_XmatsHom, const T *s_q, int tid) {\n"
+               "    using grid_rt::grid_sincos;\n    constexpr int OS = 1;\n" + _algos.code_X_single_thread(g.model) + "}\n")
+    wrappers.append('extern "C" void host_X_single_thread(double* jx, double* xh, const double* q, int tid) {\n'
+                    "    X_single_thread<double>(jx, xh, q, tid);\n}\n")
     text = "\n".join(src) + "\n".join(wrappers)
     workdir = workdir or tempfile.mkdtemp(prefix="grid_host_")
     cpp = os.path.join(workdir, f"inner_{robot.name}.cpp")

@@ -27,7 +27,7 @@ def test_library_exports_header_symbols(name):
     lib.grid_robot_name.restype = ctypes.c_char_p
     assert lib.grid_robot_name().decode() == name
     assert lib.grid_num_joints() == 2
-    assert lib.grid_abi_version() == 5
+    assert lib.grid_abi_version() == 6
     assert lib.grid_num_ees() == 1 and lib.grid_has_second_order() == 1
     lib.grid_kernel_info.restype = ctypes.c_long
     smem = lib.grid_kernel_info(6, 0, 0)
@@ -68,6 +68,6 @@ def test_generator_api_surface(tmp_path):
                  "forward_dynamics_gradient_single_timing", "forward_dynamics_gradient_compute_only",
                  "init_robotModel", "init_gridData", "init_grid", "close_grid", "FD_DU_DYNAMIC_SHARED_MEM_COUNT",
                  "NUM_JOINTS = 3", "cp.async.bulk", "aba_kernel", "crba_kernel", "idsva_so_kernel", "fdsva_so_kernel",
-                 "idsva_so_host", "end_effector_pose_kernel", "forward_dynamics_linearization_kernel", "d_fd_lin", "end_effector_pose_gradient_hessian_kernel",
+                 "idsva_so_host", "end_effector_pose_kernel", "joint_transforms_kernel", "X_single_thread", "X_warp", "forward_dynamics_linearization_kernel", "d_fd_lin", "end_effector_pose_gradient_hessian_kernel",
                  "__ffma2_rn"):
         assert name in txt, name

@@ -114,3 +114,35 @@ def test_emitter_variants_match_golden(name, env, golden, tmp_path, monkeypatch)
         lin = call(lib, gen, "forward_dynamics_linearization", 3 * n * n + n, q, qd, u)
         assert rel_err([lin[:2 * n * n]], [cm(g_["df_du"][k])]) < 1e-9
         assert rel_err([lin[2 * n * n:3 * n * n]], [cm(g_["Minv"][k])]) < 1e-9
+
+
+@pytest.mark.parametrize("name", ["chain3", "branched6", "iiwa14", "hyq"])
+def test_joint_transforms_and_fixed_target_bodies(name, golden, tmp_path):
+    """joint_transforms / X_single_thread (reference algorithms/_eepose_gradient_hessian.py:1226-1398) and the EE
+    functions of a fixed kinematic target (:31-38, :89-93) against the sympy fixtures (exact derivatives)."""
+    import ctypes
+    g_ = golden(name)
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    lib, gen = build_host_inners(robot, str(tmp_path))
+    x = g_["x"]
+    dp = ctypes.POINTER(ctypes.c_double)
+    for k in range(x.shape[0]):
+        q = np.ascontiguousarray(x[k, :n])
+        want = g_["joint_xforms"][k].transpose(0, 2, 1).reshape(-1)              # column-major 4 x 4 per joint
+        assert rel_err([call(lib, gen, "joint_transforms", 16 * n, q)], [want]) < 1e-12
+        for tid in (n - 1, n // 2, 0, n + 5):
+            jx, xh = np.full(16 * n, 7.0), np.full(16 * n, 7.0)
+            lib.host_X_single_thread.restype = None
+            lib.host_X_single_thread(jx.ctypes.data_as(dp), xh.ctypes.data_as(dp), q.ctypes.data_as(dp), ctypes.c_int(tid))
+            upto = min(tid, n - 1) + 1
+            assert np.abs(jx[:16 * upto] - want[:16 * upto]).max() < 1e-12
+            assert np.all(jx[16 * upto:] == 7.0)                                  # joints beyond tid are not touched
+        if "ft_name" in g_:
+            ft = str(g_["ft_name"])
+            assert gen.fixed_target_name == ft
+            assert rel_err([call(lib, gen, f"end_effector_pose_{ft}", 6, q)], [g_["ft_pose"][k]]) < 1e-12
+            grad = call(lib, gen, f"end_effector_pose_gradient_{ft}", 6 * n, q).reshape(n, 6).T      # [o][j]
+            assert rel_err([grad], [g_["ft_grad"][k]]) < 1e-10
+            hess = call(lib, gen, f"end_effector_pose_gradient_hessian_{ft}", 6 * n * n, q).reshape(6, n, n)
+            assert rel_err([hess], [g_["ft_hess"][k]]) < 1e-9

@@ -60,6 +60,7 @@ def test_host_tier_program_matches_c_abi(name, tmp_path):
         lib.end_effector_pose(q_qd_u),                                        # 12
         lib.end_effector_pose_gradient(q),                                    # 13
         lib.inverse_dynamics(q_qd_u),                                         # 14: raw kernel launch
+        lib.joint_transforms(q),                                              # 15
     ]
     off = 0
     for i, w in enumerate(want):

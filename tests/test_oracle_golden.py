@@ -100,3 +100,19 @@ def test_oracle_end_effector_matches_sympy_golden(name, golden):
     assert rel_err(grad, g["ee_grad"]) < 1e-7
     if "ee_hess" in g:
         assert rel_err(orc.batch_ee_pose_hessian(x[:, :n]), g["ee_hess"].reshape(K, -1)) < 1e-5
+
+
+@pytest.mark.parametrize("name", ROBOTS)
+def test_oracle_joint_transforms_and_fixed_target_match_sympy_golden(name, golden):
+    """Cumulative joint transforms (reference X_single_thread / X_warp, algorithms/_eepose_gradient_hessian.py:1226-1398)
+    and the pose of a fixed kinematic target (:31-38) against the sympy fixtures of tools/make_golden.py."""
+    g = golden(name)
+    robot = load_robot(name)
+    n = robot.get_num_pos()
+    orc = Oracle(robot)
+    x = g["x"]
+    K = len(x)
+    want = g["joint_xforms"].transpose(0, 1, 3, 2).reshape(K, 16 * n)          # column-major 4 x 4 per joint
+    assert rel_err(orc.batch_joint_transforms(x[:, :n]), want) < 1e-12
+    if "ft_name" in g:
+        assert rel_err(orc.batch_fixed_target_pose(x[:, :n], str(g["ft_name"])), g["ft_pose"]) < 1e-12

@@ -29,7 +29,9 @@ lambdified sympy matrices (what URDFParser itself does); the arithmetic executed
 End-effector pose (ee_* arrays) -- from the robot's sympy homogeneous transforms
 (`get_Xmats_hom_ordered_by_id`, the reference's input: helpers/_topology_helpers.py:76-78): chain product down to
 each leaf, pose = [x y z roll pitch yaw] with the reference's formulas
-(algorithms/_eepose_gradient_hessian.py:150-157), gradient and Hessian by sympy differentiation.
+(algorithms/_eepose_gradient_hessian.py:150-157), gradient and Hessian by sympy differentiation.  joint_xforms: the
+cumulative transforms base <- joint j (reference X_single_thread / X_warp, :1226-1398).  ft_*: pose / gradient / Hessian
+of the robot's first fixed joint as a fixed kinematic target (:31-38, :89-93).
 """
 import contextlib
 import io
@@ -53,7 +55,7 @@ KNOTS = {"atlas": 4}
 DEFAULT_KNOTS = 8
 SO_KNOTS = 3
 SO_MAX_JOINTS = 12
-EE_HESSIAN_MAX_JOINTS = 16
+EE_HESSIAN_MAX_JOINTS = 64
 H = 1e-30
 
 
@@ -133,8 +135,15 @@ def second_order(g, n, q, qd, qdd, u):
     return ids, fds
 
 
-def ee_functions(robot, order):
-    """Lambdified (pose, gradient, Hessian) of every leaf link, from the sympy homogeneous transforms."""
+def _pose_exprs(M):
+    roll = sp.atan2(M[2, 1], M[2, 2])
+    pitch = -sp.atan2(M[2, 0], sp.sqrt(M[2, 1] ** 2 + M[2, 2] ** 2))
+    yaw = sp.atan2(M[1, 0], M[0, 0])
+    return [M[0, 3], M[1, 3], M[2, 3], roll, pitch, yaw]
+
+
+def chain_transforms(robot):
+    """sympy base <- joint j transforms (4 x 4) in symbols q0..q{n-1}, following the parent topology."""
     n = robot.get_num_pos()
     qs = sp.symbols(f"q0:{n}")
     Xh = [M.subs(THETA, qs[j]) for j, M in enumerate(robot.get_Xmats_hom_ordered_by_id())]
@@ -142,22 +151,41 @@ def ee_functions(robot, order):
     for j in range(n):
         p = robot.get_parent_id(j)
         T[j] = Xh[j] if p < 0 else T[p] * Xh[j]
-    poses = []
-    for e in robot.get_leaf_nodes():
-        M = T[e]
-        roll = sp.atan2(M[2, 1], M[2, 2])
-        pitch = -sp.atan2(M[2, 0], sp.sqrt(M[2, 1] ** 2 + M[2, 2] ** 2))
-        yaw = sp.atan2(M[1, 0], M[0, 0])
-        poses += [M[0, 3], M[1, 3], M[2, 3], roll, pitch, yaw]
+    return qs, T
+
+
+def pose_functions(qs, poses, order):
+    """Lambdified (pose, gradient, Hessian) of a list of pose expressions; derivatives are only formed with respect to
+    the joints an expression depends on (the rest are structural zeros), which keeps Atlas tractable."""
+    n = len(qs)
     fpose = sp.lambdify(qs, poses, "numpy", cse=True)
     fgrad = fhess = None
     if order >= 1:
-        grads = [[sp.diff(p, qs[j]) for j in range(n)] for p in poses]
+        grads = [[(sp.diff(p, qs[j]) if qs[j] in p.free_symbols else sp.Integer(0)) for j in range(n)] for p in poses]
         fgrad = sp.lambdify(qs, grads, "numpy", cse=True)
         if order >= 2:
-            hess = [[[sp.diff(grads[o][i], qs[j]) for j in range(n)] for i in range(n)] for o in range(len(poses))]
+            hess = [[[(sp.diff(grads[o][i], qs[j]) if qs[j] in grads[o][i].free_symbols else sp.Integer(0))
+                      for j in range(n)] for i in range(n)] for o in range(len(poses))]
             fhess = sp.lambdify(qs, hess, "numpy", cse=True)
     return fpose, fgrad, fhess
+
+
+def ee_functions(robot, order):
+    """Lambdified (pose, gradient, Hessian) of every leaf link, from the sympy homogeneous transforms."""
+    qs, T = chain_transforms(robot)
+    poses = []
+    for e in robot.get_leaf_nodes():
+        poses += _pose_exprs(T[e])
+    return pose_functions(qs, poses, order)
+
+
+def fixed_target_functions(robot, fj, order):
+    """The same for ONE fixed kinematic target (reference algorithms/_eepose_gradient_hessian.py:31-38, :89-93): the
+    chain of the fixed joint's parent body times the fixed joint's constant transform."""
+    qs, T = chain_transforms(robot)
+    p = fj.parent_joint_id
+    M = fj.Xhom_sympy() if p < 0 else T[p] * fj.Xhom_sympy()
+    return pose_functions(qs, _pose_exprs(M), order)
 
 
 def main():
@@ -218,6 +246,18 @@ def main():
         if fhess is not None:
             out["ee_hess"] = np.stack([np.array(fhess(*x[k, :n]), dtype=np.float64) for k in range(K)])      # [k][6*ee + o][i][j]
         assert out["ee_pose"].shape == (K, 6 * ne)
+        # cumulative joint transforms (what the reference's X_single_thread / X_warp accumulate, :1226-1398)
+        qs, T = chain_transforms(robot)
+        fT = sp.lambdify(qs, [T[j] for j in range(n)], "numpy", cse=True)
+        out["joint_xforms"] = np.stack([np.array(fT(*x[k, :n]), dtype=np.float64).reshape(n, 4, 4) for k in range(K)])
+        # first fixed joint of the robot as a fixed kinematic target
+        if robot.fixed_joints:
+            fj = robot.fixed_joints[0]
+            fp, fg, fh = fixed_target_functions(robot, fj, 2)
+            out["ft_name"] = np.array(fj.get_name())
+            out["ft_pose"] = np.stack([np.array(fp(*x[k, :n]), dtype=np.float64) for k in range(K)])
+            out["ft_grad"] = np.stack([np.array(fg(*x[k, :n]), dtype=np.float64) for k in range(K)])
+            out["ft_hess"] = np.stack([np.array(fh(*x[k, :n]), dtype=np.float64) for k in range(K)])
         np.savez_compressed(os.path.join(outdir, name + ".npz"), **out)
         print(name, {k: v.shape for k, v in out.items()}, flush=True)
 
