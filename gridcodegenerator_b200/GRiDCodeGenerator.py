@@ -181,9 +181,21 @@ def _bind(key: str):
     def driver(self, use_thread_group=False):
         self._gen_algo(key)
 
-    def function_call(self, *a, **k):
-        raise NotImplementedError("inner functions are per-thread straight-line code in this back end; "
-                                  "call <algo>_inner<T, NT>(o, inputs..., S, gravity) directly")
+    def function_call(self, use_thread_group=False, updated_var_names=None, variant=None, **k):
+        """Emit the call of <algo>_inner as this back end defines it (reference gen_<algo>_inner_function_call, e.g.
+        algorithms/_inverse_dynamics.py:323-346, prints the call of ITS inner function with shared-memory pointers):
+            <algo>_inner<T, NT>(o, q, qd, ..., S, gravity);
+        one thread = one knot point; o / inputs point at this knot's rows, S is the thread's state base (element i at
+        S[i*NT]).  updated_var_names renames arguments: keys "o", "S", "gravity" and the input names of the variant
+        (q, qd, qdd, u, Minv).  variant selects an overload ("inverse_dynamics_qdd", ...); default: the first."""
+        names = self._variants(key)
+        if not names:
+            raise ValueError(f"{key} is not generated for this robot")
+        sp = self._specs[variant or names[0]]
+        ren = dict(updated_var_names or {})
+        args = [ren.get("o", "o")] + [ren.get(p_, p_) for p_ in sp.inner_inputs] + [ren.get("S", "S")]
+        args.append(ren.get("gravity", "gravity") if sp.uses_gravity else "T(0)")
+        self.gen_add_code_line(f"{sp.fn}_inner<T, NT>({', '.join(args)});")
 
     return temp_mem_size, inner, device, kernel, host, driver, function_call
 

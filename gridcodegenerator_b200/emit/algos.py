@@ -1555,14 +1555,15 @@ def split_phase_a_regs_policy(n: int) -> bool:
 
 
 def split_publish_Iv_policy(n: int) -> bool:
-    """Publish I v per joint (6 n state slots) or let the column functions recompute it from v.  Big robots recompute:
-    Atlas' published state drops from 931 to 751 slots (119 -> 96 KB per 32-knot tile), which is what lets TWO CTAs
-    reside on an SM -- the split kernels of big robots are bound by per-warp instruction-fetch latency, so resident warps
-    are throughput -- for ~6 % more operations."""
+    """Publish I v per joint (6 n state slots) or let the column functions recompute it from v
+    (GRID_SPLIT_PUBLISH_IV=0).  Measured on B200 for Atlas (profiles/r02d_atlas_ab.log): recomputing shrinks the
+    published state from 931 to 756 slots, enough for two resident CTAs per SM at 128 registers, but costs ~5 % more
+    operations and the 128-register column functions spill to L2: 174 us against 185 us at 8 192 knots, 1 839 us
+    against 1 288 us at 65 536.  Published everywhere."""
     mode = os.environ.get("GRID_SPLIT_PUBLISH_IV", "auto")
     if mode in ("0", "1"):
         return mode == "1"
-    return n <= 16          # HyQ (12 joints, 36 KB of state) keeps it: recomputing would cost 9 % for nothing
+    return True
 
 
 def _split_columns(cx: Ctx, sink_factory):

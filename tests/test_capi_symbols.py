@@ -60,6 +60,12 @@ def test_generator_api_surface(tmp_path):
         for tier in ("_inner", "_device", "_kernel", "_host", ""):
             assert callable(getattr(g, f"gen_{algo}{tier}")), (algo, tier)
         assert getattr(g, f"gen_{algo}_inner_temp_mem_size")() >= 0
+    # the call-line generators emit this back end's inner-function calls (reference gen_<algo>_inner_function_call)
+    g.code_str = ""
+    g.gen_forward_dynamics_gradient_inner_function_call(updated_var_names={"o": "s_df_du", "q": "s_q"})
+    g.gen_inverse_dynamics_inner_function_call(variant="inverse_dynamics_qdd")
+    assert g.code_str == ("forward_dynamics_gradient_inner<T, NT>(s_df_du, s_q, qd, u, S, gravity);\n"
+                          "inverse_dynamics_inner<T, NT>(o, q, qd, qdd, S, gravity);\n")
     path = g.gen_all_code(output_dir=str(tmp_path))
     txt = open(path).read()
     assert path.endswith("mygrid.cuh") and "namespace mygrid {" in txt
