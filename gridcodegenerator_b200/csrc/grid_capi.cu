@@ -188,8 +188,10 @@ inline void* mapped_device_pointer(const void* h) {
     if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
-template <typename T, class Launch>
-int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int out_per_knot, int nk, Launch launch) {
+// launch2(d_in, d_in2, d_out, knots, stream); h_in2 (in2_per_knot values per knot, dense) may be null
+template <typename T, class Launch2>
+int host_pipeline2(const char* fn, const T* h_in, int in_per_knot, const T* h_in2, int in2_per_knot, T* h_out,
+                   int out_per_knot, int nk, Launch2 launch2) {
     if (nk < 0 || (nk > 0 && (!h_in || !h_out))) return bad_arg(fn, "bad pointer / num_knots");
     if (nk == 0) return 0;
     HostWork* wp = host_work();
@@ -200,19 +202,22 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
     static const int zero_copy = env_int("GRID_HOST_ZEROCOPY", 0);
     if (zero_copy) {
         T* m_in = static_cast<T*>(mapped_device_pointer(h_in));
+        T* m_in2 = h_in2 ? static_cast<T*>(mapped_device_pointer(h_in2)) : nullptr;
         T* m_out = static_cast<T*>(mapped_device_pointer(h_out));
-        if (m_in && m_out) {
+        if (m_in && m_out && (!h_in2 || m_in2)) {
             if ((e = w.ensure(0, 0, 0)) != cudaSuccess) return fail(e, fn);
-            int rc = launch(m_in, m_out, nk, w.streams[0]);
+            int rc = launch2(m_in, m_in2, m_out, nk, w.streams[0]);
             if (rc) return rc;
             return fail(cudaStreamSynchronize(w.streams[0]), fn);
         }
     }
-    e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), 0, size_t(nk) * out_per_knot * sizeof(T));
+    e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), h_in2 ? size_t(nk) * in2_per_knot * sizeof(T) : 0,
+                 size_t(nk) * out_per_knot * sizeof(T));
     if (e != cudaSuccess) return fail(e, fn);
     // multiple of the 32-knot tile: every chunk stays TMA-aligned
     static const int chunk = ((env_int("GRID_HOST_CHUNK", 8192) + 31) / 32) * 32;
     T* d_in = static_cast<T*>(w.d_in);
+    T* d_in2 = h_in2 ? static_cast<T*>(w.d_in2) : nullptr;
     T* d_out = static_cast<T*>(w.d_out);
     int i = 0;
     for (int k0 = 0; k0 < nk; k0 += chunk, i++) {
@@ -221,7 +226,13 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
         e = cudaMemcpyAsync(d_in + size_t(k0) * in_per_knot, h_in + size_t(k0) * in_per_knot,
                             size_t(c) * in_per_knot * sizeof(T), cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) return fail(e, fn);
-        int rc = launch(d_in + size_t(k0) * in_per_knot, d_out + size_t(k0) * out_per_knot, c, st);
+        if (h_in2) {
+            e = cudaMemcpyAsync(d_in2 + size_t(k0) * in2_per_knot, h_in2 + size_t(k0) * in2_per_knot,
+                                size_t(c) * in2_per_knot * sizeof(T), cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return fail(e, fn);
+        }
+        int rc = launch2(d_in + size_t(k0) * in_per_knot, h_in2 ? d_in2 + size_t(k0) * in2_per_knot : nullptr,
+                         d_out + size_t(k0) * out_per_knot, c, st);
         if (rc) return rc;
         e = cudaMemcpyAsync(h_out + size_t(k0) * out_per_knot, d_out + size_t(k0) * out_per_knot,
                             size_t(c) * out_per_knot * sizeof(T), cudaMemcpyDeviceToHost, st);
@@ -230,6 +241,11 @@ int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int 
     for (int s = 0; s < 3; s++)
         if ((e = cudaStreamSynchronize(w.streams[s])) != cudaSuccess) return fail(e, fn);
     return 0;
+}
+template <typename T, class Launch>
+int host_pipeline(const char* fn, const T* h_in, int in_per_knot, T* h_out, int out_per_knot, int nk, Launch launch) {
+    return host_pipeline2<T>(fn, h_in, in_per_knot, static_cast<const T*>(nullptr), 0, h_out, out_per_knot, nk,
+        [&launch](const T* di, const T*, T* dout, int c, cudaStream_t st) { return launch(di, dout, c, st); });
 }
 
 #define GRID_INFO(CFG, ALGO, KPTR)                                                                                \
@@ -304,7 +320,10 @@ long info_core(int algo, int what) {
     extern "C" int grid_direct_minv_##SUF(const T* a, int st, T* o, int nk, void* s) {                             \
         return direct_minv_impl<T>(a, st, o, nk, s); }                                                             \
     extern "C" int grid_forward_dynamics_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {                   \
-        return forward_dynamics_impl<T>(a, st, o, nk, g, s); }
+        return forward_dynamics_impl<T>(a, st, o, nk, g, s); }                                                     \
+    extern "C" int grid_direct_minv_host_##SUF(const T* h_q, T* h_Minv, int nk) {                                  \
+        return host_pipeline<T>("grid_direct_minv_host", h_q, N, h_Minv, N * N, nk,                                \
+            [](const T* di, T* dout, int c, cudaStream_t st) { return direct_minv_impl<T>(di, N, dout, c, st); }); }
 GRID_FOR_DTYPES(X_CORE)
 
 #if (GRID_DTYPES & 1)
@@ -406,7 +425,11 @@ long info_id_du(int algo, int what) {
 #define X_ID_DU(SUF, T)                                                                                            \
     long grid_capi_info_id_du_##SUF(int algo, int what) { return info_id_du<T>(algo, what); }                      \
     extern "C" int grid_inverse_dynamics_gradient_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) { \
-        return inverse_dynamics_gradient_impl<T>(a, st, b, o, nk, g, s); }
+        return inverse_dynamics_gradient_impl<T>(a, st, b, o, nk, g, s); }                                         \
+    extern "C" int grid_inverse_dynamics_gradient_host_##SUF(const T* h_q_qd, const T* h_qdd, T* h_out, int nk, T g) { \
+        return host_pipeline2<T>("grid_inverse_dynamics_gradient_host", h_q_qd, 2 * N, h_qdd, N, h_out, 2 * N * N, nk, \
+            [g](const T* di, const T* dq, T* dout, int c, cudaStream_t st) {                                       \
+                return inverse_dynamics_gradient_impl<T>(di, 2 * N, dq, dout, c, g, st); }); }
 GRID_FOR_DTYPES(X_ID_DU)
 #endif
 
@@ -525,7 +548,13 @@ long info_aba_crba(int algo, int what) {
 #define X_ABA_CRBA(SUF, T)                                                                                         \
     long grid_capi_info_aba_crba_##SUF(int algo, int what) { return info_aba_crba<T>(algo, what); }                \
     extern "C" int grid_aba_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return aba_impl<T>(a, st, o, nk, g, s); } \
-    extern "C" int grid_crba_##SUF(const T* a, int st, T* o, int nk, void* s) { return crba_impl<T>(a, st, o, nk, s); }
+    extern "C" int grid_crba_##SUF(const T* a, int st, T* o, int nk, void* s) { return crba_impl<T>(a, st, o, nk, s); } \
+    extern "C" int grid_aba_host_##SUF(const T* h_in, T* h_qdd, int nk, T g) {                                     \
+        return host_pipeline<T>("grid_aba_host", h_in, 3 * N, h_qdd, N, nk,                                        \
+            [g](const T* di, T* dout, int c, cudaStream_t st) { return aba_impl<T>(di, 3 * N, dout, c, g, st); }); } \
+    extern "C" int grid_crba_host_##SUF(const T* h_q, T* h_M, int nk) {                                            \
+        return host_pipeline<T>("grid_crba_host", h_q, N, h_M, N * N, nk,                                          \
+            [](const T* di, T* dout, int c, cudaStream_t st) { return crba_impl<T>(di, N, dout, c, st); }); }
 GRID_FOR_DTYPES(X_ABA_CRBA)
 #endif
 
@@ -546,6 +575,9 @@ GRID_FOR_DTYPES(X_ABA_CRBA)
     }
 #define X_SO_STUB(NAME, SUF, T)                                                                                    \
     long grid_capi_info_##NAME##_##SUF(int, int) { return -1; }                                                    \
+    extern "C" int grid_##NAME##_so_host_##SUF(const T*, T*, int, T) {                                             \
+        grid_capi_last_error() = "grid_" #NAME "_so_host: this library was built without second-order kernels";    \
+        return static_cast<int>(cudaErrorNotSupported); }                                                          \
     extern "C" int grid_##NAME##_so_##SUF(const T*, int, T*, int, T, void*) {                                      \
         grid_capi_last_error() = "grid_" #NAME "_so: this library was built without second-order kernels";         \
         return static_cast<int>(cudaErrorNotSupported); }
@@ -555,7 +587,10 @@ GRID_FOR_DTYPES(X_ABA_CRBA)
 X_SO(idsva_so, idsva_so_launch, idsva_so_cfg, idsva_so_algo, idsva_so_kernel, 10)
 #define X_IDSVA(SUF, T)                                                                                            \
     long grid_capi_info_idsva_##SUF(int algo, int what) { return info_idsva_so<T>(algo, what); }                   \
-    extern "C" int grid_idsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return idsva_so_impl<T>(a, st, o, nk, g, s); }
+    extern "C" int grid_idsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return idsva_so_impl<T>(a, st, o, nk, g, s); } \
+    extern "C" int grid_idsva_so_host_##SUF(const T* h_in, T* h_out, int nk, T g) {                                \
+        return host_pipeline<T>("grid_idsva_so_host", h_in, 3 * N, h_out, 4 * N * N * N, nk,                       \
+            [g](const T* di, T* dout, int c, cudaStream_t st) { return idsva_so_impl<T>(di, 3 * N, dout, c, g, st); }); }
 #else
 #define X_IDSVA(SUF, T) X_SO_STUB(idsva, SUF, T)
 #endif
@@ -567,7 +602,10 @@ GRID_FOR_DTYPES(X_IDSVA)
 X_SO(fdsva_so, fdsva_so_launch, fdsva_so_cfg, fdsva_so_algo, fdsva_so_kernel, 11)
 #define X_FDSVA(SUF, T)                                                                                            \
     long grid_capi_info_fdsva_##SUF(int algo, int what) { return info_fdsva_so<T>(algo, what); }                   \
-    extern "C" int grid_fdsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return fdsva_so_impl<T>(a, st, o, nk, g, s); }
+    extern "C" int grid_fdsva_so_##SUF(const T* a, int st, T* o, int nk, T g, void* s) { return fdsva_so_impl<T>(a, st, o, nk, g, s); } \
+    extern "C" int grid_fdsva_so_host_##SUF(const T* h_in, T* h_out, int nk, T g) {                                \
+        return host_pipeline<T>("grid_fdsva_so_host", h_in, 3 * N, h_out, 4 * N * N * N, nk,                       \
+            [g](const T* di, T* dout, int c, cudaStream_t st) { return fdsva_so_impl<T>(di, 3 * N, dout, c, g, st); }); }
 #else
 #define X_FDSVA(SUF, T) X_SO_STUB(fdsva, SUF, T)
 #endif

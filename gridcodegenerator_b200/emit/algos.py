@@ -1674,6 +1674,14 @@ def split_forward_dynamics_gradient(model: Model, linearization: bool = False) -
             tree = _tree_of(model, c_)
             Ll = {k_: e.load(("L",) + k_) for k_ in L_all if k_[0] in tree}
             Dl = [e.load(("Dinv2", i_, 0)) if i_ in tree else ZERO for i_ in range(n)]
+            if all(not isinstance(d_, tuple) for d_ in dc):
+                # packed columns (GRID_EMIT_PAIRS): the dq and dqd halves go through the solve as one pair
+                x = ltdl_solve(cc, Ll, Dl, dc, sign=-1.0, joints=tree)
+                for r in range(n):
+                    a_, b_ = _halves(e, x[r])
+                    _out(e, c_ * n + r, a_)
+                    _out(e, (n + c_) * n + r, b_)
+                return
             for h in (0, 1):
                 x = ltdl_solve(cc, Ll, Dl, [_halves(e, d_)[h] for d_ in dc], sign=-1.0, joints=tree)
                 for r in range(n):

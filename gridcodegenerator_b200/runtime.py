@@ -243,6 +243,12 @@ class GRiDLibrary:
             getattr(L, f"grid_fixed_target_pose_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_fixed_target_pose_gradient_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_fixed_target_pose_gradient_hessian_{suf}").argtypes = [vp, ci, vp, vp, ci, vp]
+            getattr(L, f"grid_direct_minv_host_{suf}").argtypes = [vp, vp, ci]
+            getattr(L, f"grid_crba_host_{suf}").argtypes = [vp, vp, ci]
+            getattr(L, f"grid_aba_host_{suf}").argtypes = [vp, vp, ci, g]
+            getattr(L, f"grid_inverse_dynamics_gradient_host_{suf}").argtypes = [vp, vp, vp, ci, g]
+            getattr(L, f"grid_idsva_so_host_{suf}").argtypes = [vp, vp, ci, g]
+            getattr(L, f"grid_fdsva_so_host_{suf}").argtypes = [vp, vp, ci, g]
         L.grid_fixed_target_name.restype = ctypes.c_char_p
         self.fixed_target = L.grid_fixed_target_name().decode()
         self.has_second_order = bool(L.grid_has_second_order())
@@ -513,6 +519,40 @@ class GRiDLibrary:
             h_out = torch.empty((B, 3 * n * n + n), dtype=h_q_qd_u.dtype, pin_memory=True)
         self._check(getattr(self.lib, f"grid_forward_dynamics_linearization_host_{suf}")(h_q_qd_u.data_ptr(), h_out.data_ptr(), B, gravity))
         return h_out
+
+    def _host(self, name: str, h_in, in_cols: int, out_cols: int, *extra, h_in2=None):
+        """Generic host-buffer call: contiguous host (B, in_cols) tensor in, pinned (B, out_cols) tensor out."""
+        import torch
+        if h_in.is_cuda or not h_in.is_contiguous() or h_in.dim() != 2 or h_in.shape[1] != in_cols:
+            raise ValueError(f"expected a contiguous host (B, {in_cols}) tensor")
+        B = h_in.shape[0]
+        suf = self._suf(h_in)
+        h_out = torch.empty((B, out_cols), dtype=h_in.dtype, pin_memory=True)
+        args = [h_in.data_ptr()]
+        if name == "inverse_dynamics_gradient":
+            if h_in2 is not None and (h_in2.is_cuda or not h_in2.is_contiguous() or tuple(h_in2.shape) != (B, self.n)):
+                raise ValueError("qdd must be a contiguous host (B, n) tensor")
+            args.append(h_in2.data_ptr() if h_in2 is not None else None)
+        self._check(getattr(self.lib, f"grid_{name}_host_{suf}")(*args, h_out.data_ptr(), B, *extra))
+        return h_out
+
+    def direct_minv_host(self, h_q):
+        return self._host("direct_minv", h_q, self.n, self.n ** 2)
+
+    def crba_host(self, h_q):
+        return self._host("crba", h_q, self.n, self.n ** 2)
+
+    def aba_host(self, h_q_qd_tau, gravity: float = 9.81):
+        return self._host("aba", h_q_qd_tau, 3 * self.n, self.n, gravity)
+
+    def inverse_dynamics_gradient_host(self, h_q_qd, h_qdd=None, gravity: float = 9.81):
+        return self._host("inverse_dynamics_gradient", h_q_qd, 2 * self.n, 2 * self.n ** 2, gravity, h_in2=h_qdd)
+
+    def idsva_so_host(self, h_q_qd_qdd, gravity: float = 9.81):
+        return self._host("idsva_so", h_q_qd_qdd, 3 * self.n, 4 * self.n ** 3, gravity)
+
+    def fdsva_so_host(self, h_q_qd_u, gravity: float = 9.81):
+        return self._host("fdsva_so", h_q_qd_u, 3 * self.n, 4 * self.n ** 3, gravity)
 
     def forward_dynamics_host(self, h_q_qd_u, h_out=None, gravity: float = 9.81):
         import torch

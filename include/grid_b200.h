@@ -15,7 +15,9 @@
  *     H2D -> kernel -> D2H internally and return when the result is in h_out.
  *   - every function returns 0 on success or a cudaError_t value; grid_last_error() describes it.
  *     Nothing calls exit() (the reference's gpuErrchk does: GRiDCodeGenerator.py:279-286).
- *   - the current CUDA device of the calling thread is used.
+ *   - the current CUDA device of the calling thread is used (there is no `device` argument: like the CUDA runtime
+ *     itself the library is device-implicit, and its per-device state -- robot-model handles per (device, stream), host
+ *     workspace per device -- is keyed on cudaGetDevice(); one process may drive several GPUs from several threads).
  *   - gravity is the positive magnitude (9.81), as in the reference kernels
  *     (algorithms/_inverse_dynamics.py:123) == GRAVITY = -9.81 of _test.py:13-14.
  */
@@ -150,6 +152,22 @@ int grid_forward_dynamics_host_f32(const float *h_q_qd_u, float *h_qdd, int num_
 int grid_inverse_dynamics_host_f32(const float *h_q_qd_u, float *h_c, int num_knots, float gravity);
 /* release the cached device workspace of the host entry points and the robot model handles */
 int grid_release(void);
+
+/* ---- host-buffer variants of the remaining algorithms (the reference host functions' default mode: H2D -> kernel ->
+ * D2H, blocking; same chunked three-stream pipeline as grid_forward_dynamics_gradient_host_*).  Dense rows:
+ * h_q n, h_q_qd 2n, h_q_qd_tau / h_q_qd_qdd / h_q_qd_u 3n per knot; h_qdd (n per knot) may be NULL for qdd = 0. */
+int grid_direct_minv_host_f32(const float *h_q, float *h_Minv, int num_knots);
+int grid_direct_minv_host_f64(const double *h_q, double *h_Minv, int num_knots);
+int grid_inverse_dynamics_gradient_host_f32(const float *h_q_qd, const float *h_qdd, float *h_dc_du, int num_knots, float gravity);
+int grid_inverse_dynamics_gradient_host_f64(const double *h_q_qd, const double *h_qdd, double *h_dc_du, int num_knots, double gravity);
+int grid_aba_host_f32(const float *h_q_qd_tau, float *h_qdd, int num_knots, float gravity);
+int grid_aba_host_f64(const double *h_q_qd_tau, double *h_qdd, int num_knots, double gravity);
+int grid_crba_host_f32(const float *h_q, float *h_M, int num_knots);
+int grid_crba_host_f64(const double *h_q, double *h_M, int num_knots);
+int grid_idsva_so_host_f32(const float *h_q_qd_qdd, float *h_out, int num_knots, float gravity);
+int grid_idsva_so_host_f64(const double *h_q_qd_qdd, double *h_out, int num_knots, double gravity);
+int grid_fdsva_so_host_f32(const float *h_q_qd_u, float *h_out, int num_knots, float gravity);
+int grid_fdsva_so_host_f64(const double *h_q_qd_u, double *h_out, int num_knots, double gravity);
 
 /* ---- cumulative joint transforms: out[16*j + r + 4*c] = (base <- frame of joint j)[r][c], 4 x 4 column-major per joint
  * replaces what X_single_thread / X_warp leave in s_jointXforms (algorithms/_eepose_gradient_hessian.py:1226-1398; the

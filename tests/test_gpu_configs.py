@@ -220,3 +220,28 @@ def test_two_host_threads_two_devices(torch_cuda):
     assert not errs, errs
     for dev in (0, 1):
         assert torch.equal(res[dev][0], ref) and torch.equal(res[dev][1], ref), dev
+
+
+@pytest.mark.parametrize("name,B", [("iiwa14", 20000), ("hyq", 9000)])
+def test_host_entry_points_equal_device_entry_points(name, B, torch_cuda):
+    """Host-buffer variants of every algorithm (H2D -> kernel -> D2H inside the call, chunks on three streams): bit
+    identical to the device entry points.  B spans several 8192-knot chunks."""
+    torch = torch_cuda
+    lib = _lib(name)
+    n = lib.n
+    rng = np.random.default_rng(9)
+    x = torch.from_numpy(rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32))
+    X = x.cuda()
+    hp = lambda t: t.contiguous().pin_memory()
+    q, q_qd, qdd = x[:, :n], x[:, :2 * n], x[:, 2 * n:]
+    assert torch.equal(lib.direct_minv_host(hp(q)), lib.direct_minv(X[:, :n].contiguous()).cpu())
+    assert torch.equal(lib.crba_host(hp(q)), lib.crba(X[:, :n].contiguous()).cpu())
+    assert torch.equal(lib.aba_host(hp(x)), lib.aba(X).cpu())
+    assert torch.equal(lib.inverse_dynamics_gradient_host(hp(q_qd), hp(qdd)),
+                       lib.inverse_dynamics_gradient(X[:, :2 * n].contiguous(), X[:, 2 * n:].contiguous()).cpu())
+    assert torch.equal(lib.inverse_dynamics_gradient_host(hp(q_qd)), lib.inverse_dynamics_gradient(X[:, :2 * n].contiguous()).cpu())
+    assert torch.equal(lib.forward_dynamics_host(hp(x)), lib.forward_dynamics(X).cpu())
+    if lib.has_second_order:
+        Bs = 9000
+        assert torch.equal(lib.idsva_so_host(hp(x[:Bs])), lib.idsva_so(X[:Bs].contiguous()).cpu())
+        assert torch.equal(lib.fdsva_so_host(hp(x[:Bs])), lib.fdsva_so(X[:Bs].contiguous()).cpu())
