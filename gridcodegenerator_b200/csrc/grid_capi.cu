@@ -403,11 +403,11 @@ int grid_release(void) {
 #if HAS(PART_ID_DU)
 namespace {
 template <typename T>
-int inverse_dynamics_gradient_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_out, int nk, T g, void* s) {
+int inverse_dynamics_gradient_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_out, int nk, T g, void* s, int form = -1) {
     GRID_CHECK_ARGS("grid_inverse_dynamics_gradient", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_out)),
                     grid::inverse_dynamics_gradient_cfg<T>::NEEDS_SCRATCH || grid::inverse_dynamics_gradient_qdd_cfg<T>::NEEDS_SCRATCH);
-    return fail(d_qdd ? grid::inverse_dynamics_gradient_qdd_launch<T>(d_out, d_q_qd, stride, d_qdd, m, g, nk, st)
-                      : grid::inverse_dynamics_gradient_launch<T>(d_out, d_q_qd, stride, m, g, nk, st), fn);
+    return fail(d_qdd ? grid::inverse_dynamics_gradient_qdd_launch<T>(d_out, d_q_qd, stride, d_qdd, m, g, nk, st, form)
+                      : grid::inverse_dynamics_gradient_launch<T>(d_out, d_q_qd, stride, m, g, nk, st, form), fn);
 }
 template <typename T>
 long info_id_du(int algo, int what) {
@@ -427,9 +427,12 @@ long info_id_du(int algo, int what) {
     extern "C" int grid_inverse_dynamics_gradient_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) { \
         return inverse_dynamics_gradient_impl<T>(a, st, b, o, nk, g, s); }                                         \
     extern "C" int grid_inverse_dynamics_gradient_host_##SUF(const T* h_q_qd, const T* h_qdd, T* h_out, int nk, T g) { \
+        /* one kernel form for the whole batch (as the device entry point picks it), passed to every chunk */      \
+        const int form = h_qdd ? grid::inverse_dynamics_gradient_qdd_form_for<T>(nk)                               \
+                               : grid::inverse_dynamics_gradient_form_for<T>(nk);                                  \
         return host_pipeline2<T>("grid_inverse_dynamics_gradient_host", h_q_qd, 2 * N, h_qdd, N, h_out, 2 * N * N, nk, \
-            [g](const T* di, const T* dq, T* dout, int c, cudaStream_t st) {                                       \
-                return inverse_dynamics_gradient_impl<T>(di, 2 * N, dq, dout, c, g, st); }); }
+            [g, form](const T* di, const T* dq, T* dout, int c, cudaStream_t st) {                                 \
+                return inverse_dynamics_gradient_impl<T>(di, 2 * N, dq, dout, c, g, st, form); }); }
 GRID_FOR_DTYPES(X_ID_DU)
 #endif
 
