@@ -24,6 +24,12 @@
 
 // compiler-only memory fence used by the emitted bodies at joint / column boundaries
 #define GRID_FENCE() asm volatile("" ::"l"(S) : "memory")
+// An opaque copy of a scalar: the second-order bodies run the RNEA once per seed-pair block on laundered copies of
+// their inputs, so the compiler cannot merge the value-level work of different passes (and keep it live across the
+// whole kernel).  Costs at most a register move.
+__device__ __forceinline__ float grid_launder(float x) { asm volatile("" : "+f"(x)); return x; }
+__device__ __forceinline__ double grid_launder(double x) { asm volatile("" : "+d"(x)); return x; }
+#define GRID_LAUNDER(x) grid_launder(x)
 // Emitted once per body before its first output write (see tile_loop: the output staging buffer of a TMA-staged
 // tile is still being read by the previous tile's bulk store when the next body starts; the body's first passes
 // write no output, so the wait is deferred to this point and normally finds the store long finished).

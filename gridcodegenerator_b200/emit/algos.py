@@ -1162,6 +1162,75 @@ def rnea_second_order(cx: Ctx, qd_in: Sequence[V], qdd: Sequence[V]):
     return c
 
 
+def so_blocks_policy() -> bool:
+    """Second-order tangents in seed-pair blocks (one pass of the RNEA per pair of joints) instead of all seed pairs
+    at once.  All at once, every f_j is live with all its first- and second-order tangents at the end of the forward
+    pass (iiwa14: 2 226 values per thread -> a 9.5 KB stack, the kernels run at the L2's spill bandwidth, DESIGN.md
+    section 6); in blocks the live set of a pass is <= ~450 values for ~1.7x the arithmetic.  GRID_SO_BLOCKS=0 restores
+    the one-pass form."""
+    return os.environ.get("GRID_SO_BLOCKS", "1") != "0"
+
+
+def seed_pair_blocks(model: Model):
+    """(a, b), b <= a: the joint pairs whose (q, qd) seeds can give a non-zero second derivative of RNEA -- joints of
+    the same base-rooted tree (the trees of a fixed-base robot do not interact)."""
+    return [(a, b) for a in range(model.n) for b in range(a + 1) if b in _tree_of(model, a)]
+
+
+def _so_pass_ctx(cx: Ctx, seed_joints, tree, tag: str, qd_in, qdd):
+    """Inputs of one seed-pair pass: copies of the runtime scalars the RNEA reads, passed through GRID_LAUNDER so that
+    the compiler cannot merge the value-level work of different passes (it would keep those values live across the
+    whole kernel), with tangents only on the seeds of `seed_joints`: q_j -> seed j (through sin / cos), qd_j -> n + j."""
+    em, n = cx.em, cx.n
+    X = [None] * n
+    qd = [None] * n
+    qdd2 = [None] * n if qdd is not None else None
+    for j in sorted(tree):
+        jd = cx.m.joints[j]
+        sn0, cs0, q0 = cx.trig[j]
+        seeded = j in seed_joints
+        if jd.revolute:
+            sn = em.named(f"sn{j}_{tag}", f"GRID_LAUNDER({sn0.s})")
+            cs = em.named(f"cs{j}_{tag}", f"GRID_LAUNDER({cs0.s})")
+            if seeded:
+                nsn, ncs = em.tmp(f"-{sn.s}"), em.tmp(f"-{cs.s}")
+                sn = V(s=sn.s, d={j: V(s=cs.s, d={j: V(s=nsn.s)})})
+                cs = V(s=cs.s, d={j: V(s=nsn.s, d={j: V(s=ncs.s)})})
+            tr = Trig(sn, cs, q0)
+        else:
+            qv = em.named(f"q{j}_{tag}", f"GRID_LAUNDER({q0.s})")
+            if seeded:
+                qv = V(s=qv.s, d={j: ONE})
+            tr = Trig(None, None, qv)
+        X[j] = Xform(jd, tr)
+        v = em.named(f"qd{j}_{tag}", f"GRID_LAUNDER({qd_in[j].s})")
+        qd[j] = V(s=v.s, d={n + j: ONE}) if seeded else v
+        if qdd is not None:
+            qdd2[j] = em.named(f"qdd{j}_{tag}", f"GRID_LAUNDER({qdd[j].s})")
+    return X, qd, qdd2
+
+
+def rnea_second_order_blocks(cx: Ctx, qd_in: Sequence[V], qdd: Sequence[V], sink):
+    """The tangents of rnea_second_order, produced block by block: for every joint pair (a, b), b <= a, of a tree one
+    RNEA pass over that tree with the four seeds q_a, qd_a, q_b, qd_b and only the second-order pairs
+    {q_a, qd_a} x {q_b, qd_b}; sink(a, b, c) receives c (c[i] for the joints of the tree; c[i].d[k].d[l], l <= k)."""
+    em, n = cx.em, cx.n
+    save = (em.ad_order, em.ad_pairs, cx.X)
+    for (a, b) in seed_pair_blocks(cx.m):
+        tree = _tree_of(cx.m, a)
+        em.comment(f"==== second-order pass: seeds of joints {a} x {b}")
+        K, L = (a, n + a), (b, n + b)
+        em.ad_order = 2
+        em.ad_pairs = {(max(k, l), min(k, l)) for k in K for l in L}
+        cx.X, qd, qdd2 = _so_pass_ctx(cx, {a, b}, tree, f"p{a}_{b}", qd_in, qdd)
+        rnea_forward(cx, qd, qdd2, keep=False, fname="f2", joints=tree)
+        c = rnea_backward(cx, qd, keep_f=False, fname="f2", joints=tree)
+        em.ad_order, em.ad_pairs, cx.X = save
+        sink(a, b, c)
+        for j in tree:
+            em.release_vec("f2", j)
+
+
 def mass_matrix_gradient(cx: Ctx) -> Dict[tuple, V]:
     """M(q) by CRBA with first-order tangents: Mv[(i, j)].d[k] = dM_ij/dq_k, i <= j
     (reference output dM_dq, algorithms/_idsva_so.py:159)."""
@@ -1192,9 +1261,34 @@ def body_idsva_so(model: Model) -> Body:
     em, n = cx.em, model.n
     qd = cx.read_vec("qd", "qd_")
     qdd = cx.read_vec("qdd", "qdd_")
+    n3 = n * n * n
+    if so_blocks_policy():
+        done = set()
+
+        def put(idx, v):
+            _out(em, idx, v)
+            done.add(idx)
+
+        def sink(a, b, c):
+            for i in sorted(_tree_of(model, a)):
+                for (j, k) in ((a, b), (b, a)) if a != b else ((a, a),):
+                    idx = i * n * n + j * n + k
+                    put(idx, _d2(c[i], j, k))
+                    put(n3 + idx, _d2(c[i], n + j, n + k))
+                    put(2 * n3 + idx, _d2(c[i], n + j, k))
+
+        rnea_second_order_blocks(cx, qd, qdd, sink)
+        em.comment("---- dM/dq")
+        Mv = mass_matrix_gradient(cx)
+        for idx in range(n3):
+            for t in range(3):
+                if t * n3 + idx not in done:       # joints of different base-rooted trees: structurally zero
+                    _out(em, t * n3 + idx, ZERO)
+            i, j, k = idx // (n * n), (idx // n) % n, idx % n
+            _out(em, 3 * n3 + idx, _d1(Mv.get((min(i, j), max(i, j)), ZERO), k))
+        return Body("idsva_so_inner", "", cx, "second-order inverse dynamics tensors (4 n^3)")
     c = rnea_second_order(cx, qd, qdd)
     Mv = mass_matrix_gradient(cx)
-    n3 = n * n * n
     for i in range(n):
         for j in range(n):
             for k in range(n):
@@ -1226,6 +1320,8 @@ def body_fdsva_so(model: Model) -> Body:
     Minv = minv_columns(cx)
     qdd = fd_finish(cx, Minv, u, c0)
     Mi = [[minv_get(Minv, r, k) for k in range(n)] for r in range(n)]
+    if so_blocks_policy():
+        return _fdsva_so_blocks(cx, qd, qdd, Mi)
     em.comment("---- RNEA(q, qd, qdd) with first and second order tangents")
     c = rnea_second_order(cx, qd, qdd)
     em.comment("---- dM/dq")
@@ -1261,6 +1357,67 @@ def body_fdsva_so(model: Model) -> Body:
             for i in range(n):
                 _out(em, 2 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in range(n)]))
                 _out(em, 3 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner_t[L]) for L in range(n)]))
+    return Body("fdsva_so_inner", "", cx, "second-order forward dynamics tensors (4 n^3)")
+
+
+def _fdsva_so_blocks(cx: Ctx, qd, qdd, Mi) -> Body:
+    """body_fdsva_so with the RNEA tangents produced in seed-pair blocks: every pass (a, b) carries the first-order
+    tangents of its four seeds, so the columns A_q[:, a], A_q[:, b], A_v[:, a], A_v[:, b] and the contractions of the
+    pairs (a, b) / (b, a) are finished inside the pass; only Minv and dM/dq stay live between passes."""
+    em, n, model = cx.em, cx.n, cx.m
+    n3 = n * n * n
+    em.comment("---- dM/dq")
+    Mv = mass_matrix_gradient(cx)
+    dM = [[[_d1(Mv.get((min(i, L), max(i, L)), ZERO), k) for k in range(n)] for L in range(n)] for i in range(n)]
+    done = set()
+
+    def put(idx, v):
+        _out(em, idx, v)
+        done.add(idx)
+
+    def sink(a, b, c):
+        tree = sorted(_tree_of(model, a))
+        ci = lambda i: c[i] if isinstance(c[i], V) else ZERO
+
+        def A(seed):       # -Minv dc/du_seed (rows of the tree; the other rows are structurally zero)
+            return {L: em.lincomb([(-1.0, Mi[L][m_], _d1(ci(m_), seed)) for m_ in tree]) for L in tree}
+
+        Aq = {a: A(a)}
+        Av = {a: A(n + a)}
+        if b != a:
+            Aq[b], Av[b] = A(b), A(n + b)
+        em.comment(f"---- contractions of the pairs ({a}, {b})")
+        # d2qdd/dq_j dq_k (symmetric in j, k)
+        inner = {L: em.lincomb([(1.0, dM[L][m_][b], Aq[a][m_]) for m_ in tree] +
+                               [(1.0, dM[L][m_][a], Aq[b][m_]) for m_ in tree], _d2(ci(L), a, b)) for L in tree}
+        for i in tree:
+            v = em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in tree])
+            put(i * n * n + a * n + b, v)
+            if a != b:
+                put(i * n * n + b * n + a, v)
+        # d2qdd/dqd_j dqd_k (symmetric)
+        for i in tree:
+            v = em.lincomb([(-1.0, Mi[i][L], _d2(ci(L), n + a, n + b)) for L in tree])
+            put(n3 + i * n * n + a * n + b, v)
+            if a != b:
+                put(n3 + i * n * n + b * n + a, v)
+        # d2qdd/dqd_j dq_k
+        for (j, k) in ((a, b), (b, a)) if a != b else ((a, a),):
+            inner = {L: em.lincomb([(1.0, dM[L][m_][k], Av[j][m_]) for m_ in tree], _d2(ci(L), n + j, k)) for L in tree}
+            for i in tree:
+                put(2 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner[L]) for L in tree]))
+
+    em.comment("---- RNEA(q, qd, qdd) with first and second order tangents, in seed-pair blocks")
+    rnea_second_order_blocks(cx, qd, qdd, sink)
+    em.comment("---- d2qdd/dtau dq, structural zeros")
+    for j in range(n):
+        for k in range(n):
+            inner_t = [em.lincomb([(1.0, dM[L][m_][k], Mi[m_][j]) for m_ in range(n)]) for L in range(n)]
+            for i in range(n):
+                _out(em, 3 * n3 + i * n * n + j * n + k, em.lincomb([(-1.0, Mi[i][L], inner_t[L]) for L in range(n)]))
+    for idx in range(3 * n3):
+        if idx not in done:
+            _out(em, idx, ZERO)
     return Body("fdsva_so_inner", "", cx, "second-order forward dynamics tensors (4 n^3)")
 
 

@@ -85,6 +85,9 @@ class Em:
         self.ad_order = 0
         self._ad_depth = 0
         self._ad_cap = None
+        # seed-pair blocks (second order in passes): when set, only the second-order tangents (k, l), l <= k, listed
+        # here are formed; the first-order seeds are whatever the inputs carry
+        self.ad_pairs = None
 
     # ------------------------------------------------------------------ text
     def line(self, txt: str):
@@ -165,6 +168,8 @@ class Em:
             seeds.update(acc.d.keys())
         if self._ad_cap is not None:
             seeds = {k for k in seeds if k <= self._ad_cap}
+            if self.ad_pairs is not None:
+                seeds = {k for k in seeds if (self._ad_cap, k) in self.ad_pairs}
         if not seeds:
             return r
         r = V(c=r.c, s=r.s, p=r.p)          # fresh object: r may alias an input
@@ -215,7 +220,7 @@ class Em:
             rk = V(c=rk.c, s=rk.s)
             if order >= 2 and second is not None:
                 rk.d = {}
-                for l in sorted(x for x in seeds if x <= k):
+                for l in sorted(x for x in seeds if x <= k and (self.ad_pairs is None or (k, x) in self.ad_pairs)):
                     ul = [u.d.get(l) if u.d else None for u in inputs]
                     tt = []
                     for a in range(m):

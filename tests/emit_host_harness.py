@@ -19,6 +19,7 @@ PRELUDE = """
 #define __restrict__
 #define GRID_FENCE() do { } while (0)
 #define GRID_SYNC() do { } while (0)
+#define GRID_LAUNDER(x) (x)
 #define GRID_BEFORE_FIRST_OUTPUT() do { } while (0)
 namespace grid_rt {
 static inline void grid_sincos(double x, double* s, double* c) { *s = sin(x); *c = cos(x); }

@@ -36,6 +36,8 @@ def main():
     cmd = [rt._nvcc()] + [f for f in rt.NVCC_FLAGS if f not in ("-shared", "-Xcompiler", "-fPIC")] + [
         "-cubin", "-Xptxas", "-v", f"-I{out_dir}", f"-I{rt.INCLUDE}", f'-DGRID_ROBOT_NAME="{robot}"',
         f"-DGRID_PARTS={part}", f"-DGRID_DTYPES={dtype}", os.path.join(rt.CSRC, "grid_capi.cu"), "-o", cubin]
+    if part in (0x20, 0x40) and os.environ.get("GRID_SO_PTXAS_O1", "1") == "1":
+        cmd[1:1] = ["-Xptxas", "-O1"]           # as runtime._compile_part does for the second-order units
     res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if res.returncode != 0:
         print(res.stdout[-3000:])
