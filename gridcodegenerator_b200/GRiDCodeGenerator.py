@@ -109,7 +109,13 @@ class GRiDCodeGenerator:
             b = self._body(v)
             self._add_block(_hdr.emit_inner(sp, b))
             self._add_block(_hdr.emit_algo_struct(sp, b, self.model.n))
-            self._add_block(_hdr.emit_config(sp, b, self.model.n))
+            ss = (False, False)
+            if _hdr.has_split(sp, self.model.n):
+                if v not in self._sbodies:
+                    self._sbodies[v] = _hdr.split_body(sp, self.model)
+                xp = os.environ.get("GRID_SPLIT_XPOSE", "0") == "1"
+                ss = tuple(xp and _hdr.split_ntile(self._sbodies[v], sp, self.model.n, sz) > 1 for sz in (4, 8))
+            self._add_block(_hdr.emit_config(sp, b, self.model.n, ss))
             if sp.fn == "joint_transforms":
                 # the reference's helper names for the same quantity (algorithms/_eepose_gradient_hessian.py:1226-1398)
                 self._add_block(
@@ -256,6 +262,12 @@ def _scratch_constants(self):
         for size in (4, 8):
             NT, state_smem, staged = _hdr.choose_config(max(b.nslots, 1), IN, out, size)
             need = (0 if state_smem else NT * max(b.nslots, 1)) + (NT * out if staged == 3 else 0)
+            if _hdr.has_split(sp, self.model.n):      # transposed store of the multi-tile split form
+                if name not in self._sbodies:
+                    self._sbodies[name] = _hdr.split_body(sp, self.model)
+                g = _hdr.split_ntile(self._sbodies[name], sp, self.model.n, size)
+                if g > 1 and os.environ.get("GRID_SPLIT_XPOSE", "0") == "1":
+                    need = max(need, g * 32 * out)
             if size == 4:
                 per4 = max(per4, need)
             else:

@@ -553,6 +553,156 @@ __device__ __forceinline__ void tile_loop_split(const TileArgs<T>& a, unsigned c
     __syncthreads();
 }
 
+// ------------------------------------------------------------------ split tile loop, several tiles per CTA pass
+// Big robots (Atlas: 830 KB of straight-line SASS per tile) are bound by instruction supply: code beyond the ~128 KB
+// the SM's instruction caches hold streams from L2 at ~2.7 B/clk per SM, however many warps run it
+// (tools/probes/icache_stream.py, profiles/r02j_icache_stream.log), and in the split form every warp of a CTA runs
+// DIFFERENT code, so a tile costs one pass over the whole body.  Here a CTA holds the published state of A::NTILE
+// tiles in shared memory at once: phase A runs (tile, part) units concurrently on the CTA's warps (the same part of
+// two tiles on two warps at the same time -> one fetch), and in phase B every column function loops over the
+// resident tiles before the warp moves on to its next column, so a fetched column body (10-30 KB) is executed
+// NTILE times out of the instruction cache.
+// Output rows of such robots do not fit shared memory (Atlas: 225 KB per tile) and a lane writing its own row costs
+// 32 sectors per store instruction, so every lane writes its row into a lane-interleaved global scratch (element i
+// of lane l of tile t at [(t*OUT + i)*32 + l]: one full 128-byte line per store instruction, L2-resident) and after
+// phase B the CTA copies the scratch into the caller's knot-major rows through 32 x 33 transpose tiles that reuse the
+// (then dead) state area -- the same transposed store as tile_loop's STAGED == 3.
+// Batches with fewer tiles than CTAs run one tile per pass (latency first).
+template <class A, typename T>
+constexpr size_t split_multi_smem_bytes() {
+    size_t b = align16(size_t(A::NTILE) * A::SLOTS * TILE * sizeof(T));
+    for (int s = 0; s < MAX_STREAMS; s++) b += align16(size_t(A::NTILE) * TILE * in_n<A>(s) * sizeof(T));
+    return b + 32;
+}
+// scratch elements one CTA of tile_loop_split_multi addresses
+template <class A>
+constexpr size_t split_multi_scratch_elems() { return A::XPOSE ? size_t(A::NTILE) * TILE * A::OUT : 0; }
+
+template <class A, typename T>
+__device__ __forceinline__ void tile_loop_split_multi(const TileArgs<T>& a, unsigned char* smem) {
+    constexpr int NW = A::NW;
+    constexpr int NT = NW * 32;
+    constexpr size_t STATE = size_t(A::SLOTS) * TILE;          // elements of one tile's published state
+    constexpr size_t OROWS = size_t(TILE) * A::OUT;            // scratch elements of one tile's output rows
+    constexpr int NCHUNK = (A::OUT + TILE - 1) / TILE;
+    constexpr bool XP = A::XPOSE;                              // transposed store through the global scratch
+    constexpr int OS = XP ? TILE : 1;                          // element stride of the rows the bodies write
+    static_assert(A::NTILE <= 2 && NW % A::NTILE == 0, "phase B pairs the warps of a CTA over at most two tiles");
+    static_assert(size_t(A::NTILE) * STATE >= size_t(NW) * TILE * 33, "transpose tiles reuse the state area");
+    if (blockDim.x != NT) return;                  // launch contract: exactly NW warps per CTA
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int num_tiles = (a.num_knots + TILE - 1) / TILE;
+    const int G = num_tiles > int(gridDim.x) ? A::NTILE : 1;   // tiles per pass
+    const int num_groups = (num_tiles + G - 1) / G;
+    pdl_release();
+
+    T* S = reinterpret_cast<T*>(smem) + lane;
+    T* tile_s = reinterpret_cast<T*>(smem) + size_t(warp) * TILE * 33;
+    T* scr = XP ? a.scratch + size_t(blockIdx.x) * split_multi_scratch_elems<A>() : nullptr;
+    size_t off = align16(size_t(A::NTILE) * STATE * sizeof(T));
+    size_t in_off[MAX_STREAMS];
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++) {
+        in_off[s] = off;
+        off += align16(size_t(A::NTILE) * TILE * in_n<A>(s) * sizeof(T));
+    }
+    const size_t stage_end = off;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + off);
+
+    bool dense = true;
+#pragma unroll
+    for (int s = 0; s < MAX_STREAMS; s++)
+        if (in_n<A>(s)) dense = dense && a.stride[s] == in_n<A>(s) && (reinterpret_cast<uintptr_t>(a.in[s]) & 15) == 0;
+
+    {   // dummy lanes of a ragged group read whatever is in the input staging buffers: make it finite
+        T* z = reinterpret_cast<T*>(smem + in_off[0]);
+        for (size_t i = tid; i < (stage_end - in_off[0]) / sizeof(T); i += NT) z[i] = T(0);
+    }
+    if (tid == 0) mbar_init(&bar[0], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+    __syncthreads();
+    pdl_wait();                                      // first global access is below
+
+    auto group_is_tma = [&](int g) { return dense && g < num_groups && (g + 1) * G * TILE <= a.num_knots; };
+    auto issue_load = [&](int g) {                  // thread 0 only: the G tiles of a group are contiguous in the batch
+        uint32_t bytes = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++) bytes += in_n<A>(s) ? uint32_t(G * TILE * in_n<A>(s) * sizeof(T)) : 0u;
+        mbar_expect_tx(&bar[0], bytes);
+#pragma unroll
+        for (int s = 0; s < MAX_STREAMS; s++)
+            if (in_n<A>(s))
+                bulk_g2s(smem + in_off[s], a.in[s] + size_t(g) * G * TILE * in_n<A>(s),
+                         uint32_t(G * TILE * in_n<A>(s) * sizeof(T)), &bar[0]);
+    };
+
+    uint32_t phase = 0u;
+    const int first = blockIdx.x;
+    if (tid == 0 && group_is_tma(first)) issue_load(first);
+
+    for (int g = first; g < num_groups; g += gridDim.x) {
+        const int next = g + gridDim.x;
+        const bool tma = group_is_tma(g);
+        const int nt = min(G, num_tiles - g * G);            // tiles present in this group
+        // phase A: unit u = (tile t of the group, part p); the warps take units round-robin
+        for (int u = warp; u < nt * A::NA; u += NW) {
+            const int t = u / A::NA, part = u - t * A::NA;
+            int k = (g * G + t) * TILE + lane;
+            if (k >= a.num_knots) k = a.num_knots - 1;       // dummy lanes of a ragged tile redo the batch's last knot
+            const T* x[MAX_STREAMS];
+            if (tma) {
+                mbar_wait(&bar[0], phase);
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++)
+                    x[s] = reinterpret_cast<const T*>(smem + in_off[s]) + size_t(t * TILE + lane) * in_n<A>(s);
+            } else {                                          // ragged tail / strided or unaligned caller buffers
+#pragma unroll
+                for (int s = 0; s < MAX_STREAMS; s++)
+                    x[s] = in_n<A>(s) ? a.in[s] + size_t(k) * a.stride[s] : nullptr;
+            }
+            A::template phaseA<TILE, OS>(part, XP ? scr + size_t(t) * OROWS + lane : a.out + size_t(k) * A::OUT, x[0], x[1], x[2],
+                                         S + size_t(t) * STATE, a.gravity);
+        }
+        fence_proxy_async();                                  // generic reads of the input buffer before its next TMA write
+        if (tma) phase ^= 1u;
+        __syncthreads();                                      // state of every tile of the group published
+        if (tid == 0 && group_is_tma(next)) issue_load(next);
+        {
+            // phase B: with two tiles resident, warps 2i and 2i+1 run the SAME columns on tile 0 and tile 1 at the same
+            // time (one instruction fetch serves both); with one tile the two warps halve those columns between them
+            int k0 = g * G * TILE + lane, k1 = k0 + TILE;
+            if (k0 >= a.num_knots) k0 = a.num_knots - 1;
+            if (k1 >= a.num_knots) k1 = a.num_knots - 1;
+            T* o0 = XP ? scr + lane : a.out + size_t(k0) * A::OUT;
+            T* o1 = XP ? scr + OROWS + lane : a.out + size_t(k1) * A::OUT;
+            A::template phaseB_multi<TILE, OS>(warp, nt, o0, o1, S);
+        }
+        __syncthreads();                                      // every row of the group is written; state is dead
+        // XPOSE: all warps share the transposition: work item p = (tile of the group, chunk of 32 output elements)
+        for (int p = warp; XP && p < nt * NCHUNK; p += NW) {
+            const int t = p / NCHUNK, i0 = (p - t * NCHUNK) * TILE;
+            const int tile = g * G + t;
+            const int nvalid = min(TILE, a.num_knots - tile * TILE);
+            const T* src = scr + size_t(t) * OROWS + size_t(i0) * TILE + lane;
+            T v[TILE];
+#pragma unroll
+            for (int i = 0; i < TILE; i++) v[i] = (i0 + i < A::OUT) ? __ldcg(src + i * TILE) : T(0);
+#pragma unroll
+            for (int i = 0; i < TILE; i++) tile_s[i * 33 + lane] = v[i];
+            __syncwarp();
+            if (i0 + lane < A::OUT) {
+                T* d = a.out + size_t(tile) * TILE * A::OUT + i0 + lane;
+#pragma unroll 8
+                for (int l = 0; l < nvalid; l++) d[size_t(l) * A::OUT] = tile_s[lane * 33 + l];
+            }
+            __syncwarp();
+        }
+        __syncthreads();                                      // state area and scratch rows free for the next group
+    }
+}
+
 // ------------------------------------------------------------------ host side
 struct KernelPlan { const void* fn; int device; int blocks_per_sm; int sms; };
 

@@ -33,8 +33,11 @@ typedef grid::forward_dynamics_gradient_algo<float> Algo;
 
 constexpr int N = grid::NUM_JOINTS;
 constexpr int MAX_DEVICES = 16;
-constexpr int NOALLOC_MAX_BLOCKS = 32;
 constexpr int NOALLOC_MAX_KNOTS = GRID_NOALLOC_MAX_KNOTS;
+// CTAs that hold NOALLOC_MAX_KNOTS in one round of the tile loop, at most 32
+constexpr int NOALLOC_TILES = (NOALLOC_MAX_KNOTS + grid_rt::TILE - 1) / grid_rt::TILE;
+constexpr int NOALLOC_ROUND_BLOCKS = (NOALLOC_TILES + Cfg::NT / 32 - 1) / (Cfg::NT / 32);
+constexpr int NOALLOC_MAX_BLOCKS = NOALLOC_ROUND_BLOCKS < 32 ? NOALLOC_ROUND_BLOCKS : 32;
 // scratch elements one CTA of the tile loop addresses (grid_b200_runtime.cuh: tile_loop, S = a.scratch + blockIdx.x * ...)
 constexpr size_t PER_BLOCK = (Cfg::STATE_SMEM ? 0 : size_t(Cfg::NT) * Algo::SLOTS) +
                              (Cfg::STAGED == 3 ? size_t(Cfg::NT) * Algo::OUT : 0);

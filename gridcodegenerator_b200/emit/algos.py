@@ -1712,15 +1712,15 @@ def split_phase_a_regs_policy(n: int) -> bool:
 
 
 def split_publish_Iv_policy(n: int) -> bool:
-    """Publish I v per joint (6 n state slots) or let the column functions recompute it from v
-    (GRID_SPLIT_PUBLISH_IV=0).  Measured on B200 for Atlas (profiles/r02d_atlas_ab.log): recomputing shrinks the
-    published state from 931 to 756 slots, enough for two resident CTAs per SM at 128 registers, but costs ~5 % more
-    operations and the 128-register column functions spill to L2: 174 us against 185 us at 8 192 knots, 1 839 us
-    against 1 288 us at 65 536.  Published everywhere."""
+    """Publish I v per joint (6 n state slots) or let the column functions recompute it from v (~5 % more operations).
+    Big robots (n > 16) recompute: Atlas' published state shrinks from 931 to 756 slots (97 KB per tile), so a split
+    CTA holds TWO tiles at once (header.split_ntile, grid_rt::tile_loop_split_multi) and every fetched column body is
+    executed twice.  (The other use of the smaller state, two resident CTAs per SM at 128 registers, was measured and
+    rejected: profiles/r02d_atlas_ab.log, the 128-register column functions spill.)  GRID_SPLIT_PUBLISH_IV=0/1 forces."""
     mode = os.environ.get("GRID_SPLIT_PUBLISH_IV", "auto")
     if mode in ("0", "1"):
         return mode == "1"
-    return True
+    return n <= 16
 
 
 def _split_columns(cx: Ctx, sink_factory):

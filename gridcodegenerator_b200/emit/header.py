@@ -18,7 +18,7 @@ from .spatial import Model
 
 SMEM_LIMIT = 232448 - 1024   # 227 KB opt-in maximum per CTA minus the per-CTA reservation
 MAX_WARPS = int(os.environ.get("GRID_MAX_WARPS", "8"))           # 65536 registers / (255 x 32)
-MAX_WARPS_SCRATCH = 4
+MAX_WARPS_SCRATCH = int(os.environ.get("GRID_MAX_WARPS_SCRATCH", "4"))   # warps per CTA when the state lives in the global scratch
 
 
 @dataclass
@@ -169,7 +169,7 @@ def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     # State too large for >= 4 warps in shared memory (Atlas gradients): state in the global scratch, 4 warps,
     # plain stores (measured on B200 with tools/tune_config.py: Atlas grad ID 212 us against 271 us transposed and
     # 294 us with 2 warps of shared-memory state; grad FD 387 / 393 / 662 us; batch 8192).
-    return 32 * MAX_WARPS_SCRATCH, False, 0
+    return 32 * MAX_WARPS_SCRATCH, False, int(os.environ.get("GRID_SCRATCH_STAGED", "0"))
 
 
 def algo_struct_name(sp: AlgoSpec) -> str:
@@ -203,7 +203,7 @@ def emit_algo_struct(sp: AlgoSpec, body: algos.Body, n: int) -> str:
             f"        {call}\n    }}\n}};\n\n")
 
 
-def emit_config(sp: AlgoSpec, body: algos.Body, n: int) -> str:
+def emit_config(sp: AlgoSpec, body: algos.Body, n: int, split_scratch=(False, False)) -> str:
     IN = [e for _, e in sp.streams]
     out = sp.out_n(n)
     c4 = choose_config(max(body.nslots, 1), IN, out, 4)
@@ -217,7 +217,7 @@ def emit_config(sp: AlgoSpec, body: algos.Body, n: int) -> str:
             f"    static constexpr int STAGED = sizeof(T) == 4 ? {int(c4[2])} : {int(c8[2])};\n"
             f"    static constexpr size_t SMEM_BYTES = grid_rt::tile_smem_bytes<{A}<T>, T, NT, STATE_SMEM, STAGED>();\n"
             f"    // the kernel uses d_robotModel->d_scratch: at most ONE such launch may be in flight per robotModel\n"
-            f"    static constexpr bool NEEDS_SCRATCH = !STATE_SMEM || STAGED == 3;\n"
+            f"    static constexpr bool NEEDS_SCRATCH = !STATE_SMEM || STAGED == 3 || (sizeof(T) == 4 ? {b(split_scratch[0])} : {b(split_scratch[1])});   // incl. the split form's\n"
             f"}};\n\n")
 
 
@@ -297,6 +297,22 @@ def split_smem_plan(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int):
     return best or (False, 1, 1, state + ins + 32)
 
 
+def split_ntile(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> int:
+    """Tiles whose published state a split CTA holds at once (grid_rt::tile_loop_split_multi).  1 for robots whose
+    output rows are staged in shared memory (there the split form is the small-batch, latency-first form); for big
+    robots (Atlas), whose split form is the default at every batch size and bound by instruction supply, two tiles
+    when shared memory holds them: every column body fetched from L2 is then executed by two warps at once."""
+    forced = os.environ.get("GRID_SPLIT_NTILE", "")
+    if forced:
+        return max(1, int(forced))
+    if split_smem_plan(sb, sp, n, sizeof)[0]:
+        return 1
+    a16 = lambda x: (x + 15) & ~15
+    need = lambda g: a16(g * max(sb.nslots, 1) * 32 * sizeof) + sum(a16(g * 32 * e * sizeof) for _, e in sp.streams) + 32
+    # phase B pairs the CTA's warps over two tiles (even warp count needed)
+    return 2 if (need(2) <= SMEM_LIMIT and len(split_assign(sb)) % 2 == 0) else 1
+
+
 def split_out_staged(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> bool:
     return split_smem_plan(sb, sp, n, sizeof)[0]
 
@@ -333,6 +349,18 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
         calls = " ".join(f"{stem}_col{c}<T, NT, OS>(o, S);" for c in g)
         cases.append(f"            case {w}: {calls} break;")
     writes = "GRID_BEFORE_FIRST_OUTPUT" in sb.code
+    g4, g8 = split_ntile(sb, sp, n, 4), split_ntile(sb, sp, n, 8)
+    xpose = os.environ.get("GRID_SPLIT_XPOSE", "0") == "1"
+    mcases = []
+    for w in range(0, len(groups), 2):
+        # warps w and w+1: with two tiles resident both run the columns of groups w and w+1, each on its own tile (the
+        # same code at the same time: one instruction fetch); with one tile resident warp w+h runs group w+h
+        halves = []
+        for h in (0, 1):
+            if w + h < len(groups):
+                calls = " ".join(f"{stem}_col{c}<T, NT, OS>(o, St);" for c in groups[w + h])
+                halves.append(f"                if (both || h == {h}) {{ {calls} }}")
+        mcases.append(f"            case {w // 2}:\n" + "\n".join(halves) + "\n                break;")
     out.append(f"template <typename T>\nstruct {stem}_algo {{\n"
                f"    static constexpr int IN0 = {IN[0]}, IN1 = {IN[1]}, IN2 = {IN[2]};\n"
                f"    static constexpr int OUT = {sp.out_n(n)};\n"
@@ -341,6 +369,8 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
                f"    static constexpr int NA = {na};           // warps running phase A (one part each)\n"
                f"    static constexpr int NBUF = sizeof(T) == 4 ? {plan4[1]} : {plan8[1]};   // input staging buffers\n"
                f"    static constexpr bool PHASE_A_WRITES = {'true' if writes else 'false'};\n"
+               f"    static constexpr int NTILE = sizeof(T) == 4 ? {g4} : {g8};   // tiles resident per CTA pass (tile_loop_split_multi when > 1)\n"
+               f"    static constexpr bool XPOSE = {'true' if xpose else 'false'};  // multi-tile form: transposed store through the global scratch\n"
                f"    template <int NT, int OS>\n"
                f"    static __device__ __forceinline__ void phaseA(int warp, T* __restrict__ o, const T* __restrict__ x0, "
                f"const T* __restrict__ x1, const T* __restrict__ x2, T* __restrict__ S, const T gravity) {{\n"
@@ -349,7 +379,15 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
                    for p_ in range(na)) + "\n            default: break;\n        }\n    }\n"
                f"    template <int NT, int OS>\n"
                f"    static __device__ __forceinline__ void phaseB(int warp, T* __restrict__ o, T* __restrict__ S) {{\n"
-               f"        switch (warp) {{\n" + "\n".join(cases) + "\n            default: break;\n        }\n    }\n};\n\n")
+               f"        switch (warp) {{\n" + "\n".join(cases) + "\n            default: break;\n        }\n    }\n"
+               f"    // phase B over the nt (1 or 2) resident tiles of a pass: tile t's output rows are o0 / o1, its state S + t*SLOTS*NT\n"
+               f"    template <int NT, int OS>\n"
+               f"    static __device__ __forceinline__ void phaseB_multi(int warp, int nt, T* __restrict__ o0, T* __restrict__ o1, T* __restrict__ S) {{\n"
+               f"        const bool both = nt > 1;\n"
+               f"        const int h = warp & 1;\n"
+               f"        T* __restrict__ o = (both && h) ? o1 : o0;\n"
+               f"        T* __restrict__ St = (both && h) ? S + size_t(SLOTS) * NT : S;\n"
+               f"        switch (warp >> 1) {{\n" + "\n".join(mcases) + "\n            default: break;\n        }\n    }\n};\n\n")
     st4, st8 = plan4[0], plan8[0]
     b = lambda x: "true" if x else "false"
     A = f"{stem}_algo"
@@ -357,8 +395,9 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     out.append(f"template <typename T>\nstruct {stem}_cfg {{\n"
                f"    static constexpr int NT = {nw * 32};\n"
                f"    static constexpr bool OUT_STAGED = sizeof(T) == 4 ? {b(st4)} : {b(st8)};\n"
-               f"    static constexpr size_t SMEM_BYTES = grid_rt::split_smem_bytes<{A}<T>, T, OUT_STAGED>();\n"
-               f"    static constexpr bool NEEDS_SCRATCH = false;\n"
+               f"    static constexpr size_t SMEM_BYTES = {A}<T>::NTILE > 1 ? grid_rt::split_multi_smem_bytes<{A}<T>, T>()\n"
+               f"                                                          : grid_rt::split_smem_bytes<{A}<T>, T, OUT_STAGED>();\n"
+               f"    static constexpr bool NEEDS_SCRATCH = {A}<T>::NTILE > 1 && {A}<T>::XPOSE;   // transposed store through d_robotModel->d_scratch\n"
                f"    static constexpr bool FITS = SMEM_BYTES <= {SMEM_LIMIT};   // else the split kernel is never launched\n"
                f"}};\n\n")
     fill = []
@@ -371,15 +410,16 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     C = f"{stem}_cfg<T>"
     # register budget for as many resident CTAs as the fp32 shared-memory plan allows (at most two)
     # (only when that leaves >= 128 registers per thread: HyQ's 12-warp CTAs keep the whole register file)
-    two = split_maxnreg(nw, 2) if plan4[2] >= 2 else 0
+    two = split_maxnreg(nw, 2) if (plan4[2] >= 2 and g4 == 1) else 0
     bounds = f"__maxnreg__({regs or (two if two >= 128 else split_maxnreg(nw, 1))})"
     out.append(f"template <typename T>\n__global__ void {bounds}\n"
                f"{sp.fn}_split_kernel({kernel_params(sp)}) {{\n"
                f"    extern __shared__ __align__(16) unsigned char grid_smem[];\n"
                f"    grid_rt::TileArgs<T> a;\n" + "\n".join(fill) + "\n"
-               f"    a.out = {sp.out_name}; a.scratch = nullptr;\n"
+               f"    a.out = {sp.out_name}; a.scratch = d_robotModel ? d_robotModel->d_scratch : nullptr;\n"
                f"    a.gravity = {gv}; a.num_knots = NUM_TIMESTEPS;\n"
-               f"    if ({C}::FITS) grid_rt::tile_loop_split<{A}<T>, T, {C}::OUT_STAGED>(a, grid_smem);\n}}\n\n")
+               f"    if constexpr ({A}<T>::NTILE > 1) {{ if ({C}::FITS) grid_rt::tile_loop_split_multi<{A}<T>, T>(a, grid_smem); }}\n"
+               f"    else {{ if ({C}::FITS) grid_rt::tile_loop_split<{A}<T>, T, {C}::OUT_STAGED>(a, grid_smem); }}\n}}\n\n")
     # default batch size up to which the launcher prefers the split form (tools/tune_split.py measures the crossover)
     mono = choose_config(max(mono_slots, 1), [e for _, e in sp.streams], sp.out_n(n), 4)
     max_knots = (1 << 30) if not mono[1] else SPLIT_DEFAULT_MAX_KNOTS
@@ -478,6 +518,11 @@ def emit_launch(sp: AlgoSpec, n: int) -> str:
                  f"        int sblocks = grid_rt::persistent_blocks(reinterpret_cast<const void*>(skern), {SC}::NT, "
                  f"{SC}::SMEM_BYTES, num_timesteps);\n"
                  f"        if (sblocks <= 0) {{ cudaError_t e = cudaGetLastError(); return e != cudaSuccess ? e : cudaErrorLaunchOutOfResources; }}\n"
+                 f"        if ({SC}::NEEDS_SCRATCH) {{\n"
+                 f"            const int cap = grid_rt::scratch_capacity(GRID_SCRATCH_BLOCKS_PER_SM);\n"
+                 f"            if (cap <= 0 || d_robotModel == nullptr) return cudaErrorInvalidValue;\n"
+                 f"            if (sblocks > cap) sblocks = cap;\n"
+                 f"        }}\n"
                  f"        cudaError_t se = grid_rt::launch_tile_kernel(skern, sblocks, {SC}::NT, {SC}::SMEM_BYTES, stream, {', '.join(call)});\n"
                  f"        return se != cudaSuccess ? se : cudaGetLastError();\n"
                  f"    }}\n")

@@ -141,9 +141,25 @@ def build_library(robot, force: bool = False, verbose: bool = False, pool=None) 
     if own:
         pool = ThreadPoolExecutor(max_workers=min(len(CAPI_PARTS), os.cpu_count() or 1))
     try:
-        futs = [pool.submit(_compile_part, name, out_dir, part, dt, verbose) for part, dt in CAPI_PARTS]
-        futs.append(pool.submit(_compile_noalloc, name, out_dir, verbose))
+        parts = CAPI_PARTS
+        only = os.environ.get("GRID_BUILD_ONLY")       # A/B variant builds: "0x01:1,0x04:1" = just these (part, dtype) units
+        if only:
+            parts = [(int(a, 0), int(b)) for a, b in (x.split(":") for x in only.split(","))]
+        futs = [pool.submit(_compile_part, name, out_dir, part, dt, verbose) for part, dt in parts]
+        if not only:
+            futs.append(pool.submit(_compile_noalloc, name, out_dir, verbose))
         objs = [f.result() for f in futs]
+        if only:
+            # the core unit's grid_kernel_info references one (hidden) info function per unit: weak stand-ins for
+            # the units that were left out
+            stub = os.path.join(out_dir, "partial_stub.cpp")
+            names = ["core", "ee", "id_du", "aba_crba", "idsva", "fd_du_qm", "fd_lin", "fdsva", "fd_du"]
+            with open(stub, "w") as f:
+                for nm in names:
+                    for dt in ("f32", "f64"):
+                        f.write(f'__attribute__((weak, visibility("hidden"))) int grid_capi_info_{nm}_{dt}(int, int) {{ return -1; }}\n')
+            subprocess.check_call(["g++", "-fPIC", "-c", stub, "-o", stub[:-4] + ".o"])
+            objs.append(stub[:-4] + ".o")
     finally:
         if own:
             pool.shutdown()

@@ -5,6 +5,9 @@ Split form: one CTA owns one 32-knot tile; phase A (RNEA, CRBA, L^T D L, RNEA wi
 publishes the per-knot state in shared memory, then the derivative columns run concurrently on the CTA's warps
 (grid_b200_runtime.cuh: tile_loop_split; emit/algos.py: split_*).  The launchers pick it for small batches and for
 robots whose one-lane-one-knot body is instruction-fetch bound; GRID_SPLIT_MODE forces either form (read per launch).
+Atlas (fp32) holds TWO tiles per CTA pass once a batch has more tiles than CTAs (tile_loop_split_multi): 4500 knots =
+141 tiles run one tile per pass, 4775 = 150 tiles (the last one ragged) and 4832 = 151 tiles (the last pass holds a
+single tile) run two.
 """
 import os
 
@@ -56,7 +59,8 @@ class _mode:
 
 
 @pytest.mark.parametrize("name,B", [("iiwa14", 1), ("iiwa14", 31), ("iiwa14", 1024), ("iiwa14", 5000), ("hyq", 515),
-                                    ("hyq", 16384), ("atlas", 70), ("atlas", 4500), ("branched6", 97), ("slider3", 33)])
+                                    ("hyq", 16384), ("atlas", 70), ("atlas", 4500), ("atlas", 4775), ("atlas", 4832),
+                                    ("branched6", 97), ("slider3", 33)])
 def test_split_form_fp32(name, B, torch_cuda):
     torch = torch_cuda
     lib, orc = _lib(name), _oracle(name)

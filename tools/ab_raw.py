@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """A/B a variant libgrid_<robot>.so against the in-tree library through the raw C ABI (ctypes only: works for variant
-binaries that predate newer entry points).  Times grid_forward_dynamics_gradient_f32 in both kernel forms.
+binaries that predate newer entry points).  Times grid_forward_dynamics_gradient_f32 (or AB_FN=<entry point with the
+same signature>, e.g. grid_idsva_so_f32) in both kernel forms.
 
   python tools/ab_raw.py <robot> <variant.so> [batch ...]
 """
@@ -16,9 +17,12 @@ import torch  # noqa: E402
 from gridcodegenerator_b200.runtime import library_path  # noqa: E402
 
 
+FN = os.environ.get("AB_FN", "grid_forward_dynamics_gradient_f32")   # any entry point with the grad-FD signature
+
+
 def bind(path):
     L = ctypes.CDLL(path)
-    L.grid_forward_dynamics_gradient_f32.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+    getattr(L, FN).argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                                      ctypes.c_float, ctypes.c_void_p]
     L.grid_last_error.restype = ctypes.c_char_p
     return L
@@ -61,11 +65,11 @@ def main():
         for tag, L in libs.items():
             for mode in ("0", "1"):
                 os.environ["GRID_SPLIT_MODE"] = mode
-                out = torch.empty((B, 2 * n * n), dtype=torch.float32, device="cuda")
+                out = torch.empty((B, 4 * n ** 3 if "_so_" in FN else 2 * n * n), dtype=torch.float32, device="cuda")
 
                 def fn():
                     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-                    rc = L.grid_forward_dynamics_gradient_f32(x.data_ptr(), 3 * n, out.data_ptr(), B, 9.81, st)
+                    rc = getattr(L, FN)(x.data_ptr(), 3 * n, out.data_ptr(), B, 9.81, st)
                     assert rc == 0, L.grid_last_error()
                 row[f"{tag}_{'split' if mode == '1' else 'lane'}_us"] = round(timed(fn), 2)
                 outs[(tag, mode)] = out.clone()
