@@ -165,7 +165,8 @@ def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     # [idx*32 + lane]: each store instruction is one full 128-byte line), then the CTA transposes the scratch into
     # the caller's knot-major rows through 32 x 33 shared-memory tiles with coalesced reads and writes.
     if fit >= MAX_WARPS_SCRATCH:
-        return 32 * min(MAX_WARPS, fit), True, 3
+        # GRID_LARGE_OUT_PLAIN=1 (A/B): lane-strided plain stores instead of the transposed store
+        return 32 * min(MAX_WARPS, fit), True, (0 if os.environ.get("GRID_LARGE_OUT_PLAIN") == "1" else 3)
     # State too large for >= 4 warps in shared memory (Atlas gradients): state in the global scratch, 4 warps,
     # plain stores (measured on B200 with tools/tune_config.py: Atlas grad ID 212 us against 271 us transposed and
     # 294 us with 2 warps of shared-memory state; grad FD 387 / 393 / 662 us; batch 8192).

@@ -23,7 +23,41 @@ def _floats(text, n, default):
     return tuple(vals)
 
 
-def parse_urdf_string(xml_text: str, name: str | None = None) -> Robot:
+# A 6-DoF (free) joint as a chain of six one-DoF joints over five massless links: translations along x, y, z of the
+# parent frame, then rotations about x, y, z (roll, pitch, yaw applied in that order along the chain).  Every algorithm
+# of the hot path then treats a floating-base robot as the fixed-base tree it already handles -- including the
+# reference's own CPU oracle (_test.py has no floating-base branch), which is what pins these models.  Coordinates are
+# q = [x y z roll pitch yaw | joints], qd = their rates (NOT the reference emitter's quaternion + body-twist
+# convention, helpers/_topology_helpers.py:231-255, whose robot-side half lives in the un-vendored URDFParser);
+# singular at pitch = +-90 degrees like every Euler-angle base.
+FLOATING_CHAIN = (("px", "prismatic", (1.0, 0.0, 0.0)), ("py", "prismatic", (0.0, 1.0, 0.0)),
+                  ("pz", "prismatic", (0.0, 0.0, 1.0)), ("rx", "revolute", (1.0, 0.0, 0.0)),
+                  ("ry", "revolute", (0.0, 1.0, 0.0)), ("rz", "revolute", (0.0, 0.0, 1.0)))
+
+
+def _expand_floating(links: List[LinkDesc], joints: List[JointDesc]) -> List[JointDesc]:
+    """Replace every <joint type="floating"> by the six-joint chain above (five massless links are added)."""
+    out: List[JointDesc] = []
+    for jd in joints:
+        if jd.jtype != "floating":
+            out.append(jd)
+            continue
+        parent = jd.parent
+        for i, (tag, jtype, axis) in enumerate(FLOATING_CHAIN):
+            last = i == len(FLOATING_CHAIN) - 1
+            child = jd.child if last else f"{jd.child}__{tag}"
+            if not last:
+                links.append(LinkDesc(name=child))                 # massless
+            j = JointDesc(name=f"{jd.name}_{tag}", jtype=jtype, parent=parent, child=child)
+            j.axis = axis
+            if i == 0:
+                j.xyz, j.rpy = jd.xyz, jd.rpy
+            out.append(j)
+            parent = child
+    return out
+
+
+def parse_urdf_string(xml_text: str, name: str | None = None, floating_base: bool = False) -> Robot:
     root = ET.fromstring(xml_text)
     if root.tag != "robot":
         raise ValueError("not a URDF: root element is <%s>" % root.tag)
@@ -68,19 +102,34 @@ def parse_urdf_string(xml_text: str, name: str | None = None) -> Robot:
         if lim is not None:
             jd.limits = tuple(float(lim.get(k, "0")) for k in ("lower", "upper", "effort", "velocity"))
         joints.append(jd)
-    return Robot(rname, links, joints)
+    if floating_base:
+        # the root link (never a child) hangs from a new massless world link by a free joint
+        children = {j.child for j in joints}
+        roots = [l.name for l in links if l.name not in children]
+        if len(roots) != 1:
+            raise ValueError(f"floating_base=True needs exactly one root link, found {roots}")
+        links.insert(0, LinkDesc(name="floating_base_world"))
+        joints.insert(0, JointDesc(name="floating_base", jtype="floating", parent="floating_base_world", child=roots[0]))
+    had_floating = any(j.jtype == "floating" for j in joints)
+    joints = _expand_floating(links, joints)
+    robot = Robot(rname, links, joints)
+    # True when a free joint was expanded into the six-joint chain.  `floating_base` itself stays False: that flag
+    # switches consumers to the quaternion convention (reference helpers/_topology_helpers.py:231), which this is not.
+    robot.floating_base_chain = had_floating
+    return robot
 
 
-def parse_urdf(path: str, name: str | None = None) -> Robot:
+def parse_urdf(path: str, name: str | None = None, floating_base: bool = False) -> Robot:
     with open(path, "r") as f:
         txt = f.read()
-    return parse_urdf_string(txt, name or os.path.splitext(os.path.basename(path))[0])
+    return parse_urdf_string(txt, name or os.path.splitext(os.path.basename(path))[0], floating_base)
 
 
 class URDFParser:
     """Drop-in for `URDFParser().parse(path)` as used with the reference."""
 
     def parse(self, filename, alpha_tie_breaker=False, floating_base=False):
-        if floating_base:
-            raise NotImplementedError("floating-base models are out of scope (SURVEY.md section 2 row 18)")
-        return parse_urdf(filename)
+        """floating_base=True: the root link gets a free joint to the world, modelled as a six-joint chain
+        (FLOATING_CHAIN above; the returned robot is a fixed-base tree with six more joints and
+        `floating_base_chain = True`)."""
+        return parse_urdf(filename, floating_base=floating_base)

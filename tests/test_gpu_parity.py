@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 
 TOL32 = 1e-4
 TOL64 = 1e-10
-ROBOTS = ["iiwa14", "hyq", "atlas", "branched6", "slider3"]
+ROBOTS = ["iiwa14", "hyq", "atlas", "branched6", "slider3", "hyq_floating"]   # hyq_floating: SURVEY 8(f4)
 
 
 @pytest.fixture(scope="module")
@@ -125,7 +125,7 @@ def test_second_order_golden(name, golden, torch_cuda):
         assert rel_err(got, g["so_fdsva"].reshape(K2, -1)) < tol, (name, dtype, "fdsva_so")
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 128), ("iiwa14", 1024), ("iiwa14", 1000), ("hyq", 515), ("atlas", 70),
+@pytest.mark.parametrize("name,B", [("iiwa14", 128), ("iiwa14", 1024), ("iiwa14", 1000), ("hyq", 515), ("atlas", 70), ("hyq_floating", 515),
                                     ("branched6", 33), ("slider3", 31)])
 def test_fd_grad_vs_oracle_fp32(name, B, torch_cuda):
     """BASELINE configs 1-2 sizes + ragged batches: fp32 kernel vs fp64 oracle on the fp32-rounded inputs."""
@@ -146,7 +146,7 @@ def test_fd_grad_vs_oracle_fp32(name, B, torch_cuda):
                    orc.batch_rnea_grad(x64, use_qdd=True)) < TOL32
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("iiwa14", 1000), ("hyq", 515), ("atlas", 70), ("branched6", 33),
+@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("iiwa14", 1000), ("hyq", 515), ("atlas", 70), ("branched6", 33), ("hyq_floating", 97),
                                     ("slider3", 31)])
 @pytest.mark.parametrize("dtype,tol", [("float32", TOL32), ("float64", TOL64)])
 def test_fd_linearization_vs_oracle(name, B, dtype, tol, torch_cuda):
@@ -176,7 +176,8 @@ def test_fd_linearization_vs_oracle(name, B, dtype, tol, torch_cuda):
     assert lib.forward_dynamics_linearization(X[:0]).shape == (0, 3 * n * n + n)
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("hyq", 16384), ("atlas", 200), ("branched6", 97), ("slider3", 64)])
+@pytest.mark.parametrize("name,B", [("iiwa14", 1024), ("hyq", 16384), ("atlas", 200), ("branched6", 97), ("slider3", 64),
+                                    ("hyq_floating", 300)])
 def test_aba_crba_fp32(name, B, torch_cuda):
     """ABA and CRBA (reference algorithms/_aba.py, _crba.py; BASELINE configs 3 and 4).  The reference has no
     executable CPU code for them ("parity unpinned"): the oracle's textbook versions are checked
@@ -284,7 +285,7 @@ def test_aba_crba_fp64(name, B, torch_cuda):
     assert rel_err(lib.crba(X[:, :n].contiguous()).cpu().numpy(), orc.batch_crba(x)) < TOL64
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 257), ("hyq", 96), ("atlas", 40)])
+@pytest.mark.parametrize("name,B", [("iiwa14", 257), ("hyq", 96), ("atlas", 40), ("hyq_floating", 64)])
 def test_fd_grad_vs_oracle_fp64(name, B, torch_cuda):
     torch = torch_cuda
     lib, orc = _lib(name), _oracle(name)
@@ -372,7 +373,7 @@ def test_host_transports_match_device_path(env, torch_cuda):
     assert line["matches_device_path"] is True and line["batch"] == 5000
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 1), ("iiwa14", 33), ("iiwa14", 1000), ("hyq", 97), ("atlas", 40)])
+@pytest.mark.parametrize("name,B", [("iiwa14", 1), ("iiwa14", 33), ("iiwa14", 1000), ("hyq", 97), ("atlas", 40), ("hyq_floating", 70)])
 def test_output_guard_bands(name, B, torch_cuda):
     """Own bounds check (compute-sanitizer is closed on this pool): every output-writing path (TMA bulk stores,
     ragged-tail plain stores, transposed stores, global-scratch kernels) writes exactly its (B, m) rows -- guard

@@ -60,7 +60,7 @@ class _mode:
 
 @pytest.mark.parametrize("name,B", [("iiwa14", 1), ("iiwa14", 31), ("iiwa14", 1024), ("iiwa14", 5000), ("hyq", 515),
                                     ("hyq", 16384), ("atlas", 70), ("atlas", 4500), ("atlas", 4775), ("atlas", 4832),
-                                    ("branched6", 97), ("slider3", 33)])
+                                    ("branched6", 97), ("slider3", 33), ("hyq_floating", 5000)])
 def test_split_form_fp32(name, B, torch_cuda):
     torch = torch_cuda
     lib, orc = _lib(name), _oracle(name)

@@ -152,3 +152,75 @@ def test_urdfparser_facade_and_errors(tmp_path):
         parse_urdf_string(_urdf(_link("a") + _link("b")))                                  # two roots
     with pytest.raises(ValueError):
         parse_urdf_string(_urdf(_link("base") + _link("l") + _joint("j", "planar", "base", "l")))
+
+
+# ---------------------------------------------------------------- floating base
+def _floating_pair():
+    """(fixed-base HyQ, HyQ hanging from a free joint expanded into the six-joint chain)"""
+    from gridcodegenerator_b200.robot import LIBRARY_DIR, load_robot
+    fixed = load_robot("hyq")
+    floating = URDFParser().parse(os.path.join(LIBRARY_DIR, "hyq.urdf"), floating_base=True)
+    return fixed, floating
+
+
+def test_floating_base_flag_expands_the_root_into_a_six_joint_chain():
+    from gridcodegenerator_b200.robot import load_robot
+    fixed, fl = _floating_pair()
+    assert fl.get_num_pos() == fixed.get_num_pos() + 6 and fl.floating_base_chain and not fl.floating_base
+    types = [fl.get_joint_by_id(j).get_type() for j in range(6)]
+    assert types == ["prismatic"] * 3 + ["revolute"] * 3
+    S = [int(np.argmax(fl.get_S_by_id(j))) for j in range(6)]
+    assert S == [3, 4, 5, 0, 1, 2]                                   # translations x y z, then rotations x y z
+    assert fl.get_parent_id_array()[:7] == [-1, 0, 1, 2, 3, 4, 5]
+    # the five intermediate links are massless; the sixth body is the trunk
+    for j in range(5):
+        assert np.abs(np.asarray(fl.get_Imat_by_id(j), dtype=float)).max() == 0.0
+    assert np.allclose(np.asarray(fl.get_Imat_by_id(5), dtype=float), np.asarray(fixed.base_Imat, dtype=float), atol=1e-12)
+    # the shipped hyq_floating.urdf (<joint type="floating">) is the same model
+    lib = load_robot("hyq_floating")
+    assert lib.get_num_pos() == fl.get_num_pos() and lib.get_parent_id_array() == fl.get_parent_id_array()
+    q = np.random.default_rng(3).uniform(-1, 1, fl.get_num_pos())
+    for j in range(fl.get_num_pos()):
+        assert np.abs(np.asarray(lib.get_Xmat_Func_by_id(j)(q[j]), dtype=float) -
+                      np.asarray(fl.get_Xmat_Func_by_id(j)(q[j]), dtype=float)).max() < 1e-14
+
+
+def test_floating_base_dynamics_reduce_to_the_fixed_base_robot():
+    """Base pose at the origin, base at rest: the leg torques of the floating model are the fixed-base robot's; the
+    leg block of M is the fixed-base M; the base z force carries the robot's weight; and a base that is FREE
+    (zero base wrench) in free fall makes every joint torque of a motionless robot vanish."""
+    fixed, fl = _floating_pair()
+    of, ol = Oracle(fixed), Oracle(fl)
+    n = fixed.get_num_pos()
+    rng = np.random.default_rng(11)
+    mass = 53.433 + 4 * (2.93 + 2.638 + 0.881)
+    for _ in range(3):
+        q, qd, qdd = (rng.uniform(-1, 1, n) for _ in range(3))
+        z6 = np.zeros(6)
+        cl = ol.rnea(np.concatenate([z6, q]), np.concatenate([z6, qd]), np.concatenate([z6, qdd]))[0]
+        cf = of.rnea(q, qd, qdd)[0]
+        assert np.abs(cl[6:] - cf).max() < 1e-10
+        Ml, Mf = ol.crba(np.concatenate([z6, q])), of.crba(q)
+        assert np.abs(Ml[6:, 6:] - Mf).max() < 1e-10
+        assert np.abs(Ml[:3, :3] - mass * np.eye(3)).max() < 1e-9    # translations of the whole robot: total mass
+        c0 = ol.rnea(np.concatenate([z6, q]), np.zeros(n + 6), np.zeros(n + 6))[0]
+        assert abs(c0[2] - mass * G) < 1e-9 and abs(c0[0]) < 1e-9 and abs(c0[1]) < 1e-9
+        # forward dynamics of the free robot under zero generalized force: the base falls with g, joints do not move
+        base = np.concatenate([rng.uniform(-1, 1, 3), rng.uniform(-0.5, 0.5, 3)])          # any base pose
+        qdd_free = ol.fd(np.concatenate([base, q]), np.zeros(n + 6), np.zeros(n + 6))
+        # damping is zero at rest, so the only force is gravity: uniform acceleration -g along world z
+        assert np.abs(qdd_free[6:]).max() < 1e-8 and np.abs(qdd_free[3:6]).max() < 1e-8
+        assert np.abs(qdd_free[:3] - np.array([0.0, 0.0, -G])).max() < 1e-8
+
+
+def test_floating_joint_in_the_middle_of_a_tree():
+    """type="floating" is not only for the root: a free-flying payload on top of a one-joint arm."""
+    r = parse_urdf_string(_urdf(
+        _link("base") + _link("arm", 1.0, "0 0 0.2", (0.01, 0, 0, 0.01, 0, 0.002)) + _link("payload", 2.0, "0 0 0", (0.02, 0, 0, 0.02, 0, 0.02))
+        + _joint("j1", "revolute", "base", "arm", axis="0 1 0")
+        + _joint("free", "floating", "arm", "payload", xyz="0 0 0.4")))
+    assert r.get_num_pos() == 7 and r.floating_base_chain
+    names = [r.get_joint_by_id(j).get_name() for j in range(7)]
+    assert names == ["j1", "free_px", "free_py", "free_pz", "free_rx", "free_ry", "free_rz"]
+    c = Oracle(r).rnea(np.zeros(7), np.zeros(7), np.zeros(7))[0]
+    assert abs(c[3] - 2.0 * G) < 1e-10                               # the z translation carries the payload's weight

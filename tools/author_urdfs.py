@@ -83,6 +83,16 @@ def iiwa14():
 
 
 def hyq():
+    b = _hyq_body()
+    write("hyq", b)
+    # the same robot with a free joint between a massless world link and the trunk: the URDF reader expands
+    # type="floating" into a six-joint chain (robot/urdf.py: FLOATING_CHAIN) -> 18 degrees of freedom
+    fb = ('  <link name="world"/>\n  <joint name="floating_base" type="floating">\n    <parent link="world"/>\n'
+          '    <child link="trunk"/>\n    <origin xyz="0 0 0" rpy="0 0 0"/>\n  </joint>\n')
+    write("hyq_floating", fb + b)
+
+
+def _hyq_body():
     b = link("trunk", 53.433, (0.056, 0.0215, 0.00358), (1.5725, 8.5015, 9.1954, 0.03, -0.05, 0.0))
     legs = {
         "lf": (0.3735, 0.207, 1, 1),
@@ -100,7 +110,7 @@ def hyq():
         b += joint(f"{leg}_kfe_joint", "revolute", upper, lower, (0.0, 0.0, -0.35), (0, 0, 0), Y, damping=0.1, limits=(-2.44, -0.35, 150, 12))
         b += link(foot, 0.0, (0, 0, 0), (0, 0, 0))
         b += joint(f"{leg}_foot_joint", "fixed", lower, foot, (0.0, 0.0, -0.33))
-    write("hyq", b)
+    return b
 
 
 def atlas():
