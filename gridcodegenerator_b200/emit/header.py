@@ -310,8 +310,8 @@ def split_ntile(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> int
         return 1
     a16 = lambda x: (x + 15) & ~15
     need = lambda g: a16(g * max(sb.nslots, 1) * 32 * sizeof) + sum(a16(g * 32 * e * sizeof) for _, e in sp.streams) + 32
-    # phase B pairs the CTA's warps over two tiles (even warp count needed)
-    return 2 if (need(2) <= SMEM_LIMIT and len(split_assign(sb)) % 2 == 0) else 1
+    # phase B pairs the CTA's warps over two tiles (emit_split rounds the warp count up to even)
+    return 2 if need(2) <= SMEM_LIMIT else 1
 
 
 def split_out_staged(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> bool:
@@ -339,6 +339,8 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     groups = split_assign(sb)
     na = len(sb.parts)
     nw = max(len(groups), na)
+    if nw % 2 and max(split_ntile(sb, sp, n, 4), split_ntile(sb, sp, n, 8)) > 1:
+        nw += 1                  # the two-tile form pairs the warps (tile_loop_split_multi)
     plan4 = split_smem_plan(sb, sp, n, 4)
     plan8 = split_smem_plan(sb, sp, n, 8)
     IN = [e for _, e in sp.streams] + [0, 0, 0]
