@@ -227,6 +227,13 @@ GRiDCodeGenerator.gen_inverse_dynamics_device_temp_mem_size = GRiDCodeGenerator.
 GRiDCodeGenerator.gen_crba_device_temp_mem_size = GRiDCodeGenerator.gen_crba_inner_temp_mem_size  # reference _crba.py:214
 
 
+# the reference's public code-text helpers for USER kernels (README.md:44-56): thread-strided loops, serial sections,
+# barriers, per-thread selects, global <-> shared copies, compressed-column bookkeeping
+from .emit import user_helpers as _uh  # noqa: E402
+
+for _name in _uh.PUBLIC:
+    setattr(GRiDCodeGenerator, _name, getattr(_uh, _name))
+
 # ----------------------------------------------------------------- file scaffolding
 from .emit import scaffold as _sc  # noqa: E402
 
