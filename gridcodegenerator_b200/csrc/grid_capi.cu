@@ -214,13 +214,18 @@ int host_pipeline2(const char* fn, const T* h_in, int in_per_knot, const T* h_in
     e = w.ensure(size_t(nk) * in_per_knot * sizeof(T), h_in2 ? size_t(nk) * in2_per_knot * sizeof(T) : 0,
                  size_t(nk) * out_per_knot * sizeof(T));
     if (e != cudaSuccess) return fail(e, fn);
-    // multiple of the 32-knot tile: every chunk stays TMA-aligned
-    static const int chunk = ((env_int("GRID_HOST_CHUNK", 8192) + 31) / 32) * 32;
+    // Chunk sizes are multiples of the 32-knot tile (every chunk stays TMA-aligned).  The step is bound by the
+    // device->host copies: 25.7 MB per iiwa14 step leave in 0.52 ms as ONE copy with the input copy running beside it and
+    // in 0.54 ms as eight (tools/d2h_probe.py, profiles/r02v_d2h_probe.log); the pipeline below takes 0.557 ms with equal
+    // chunks of 8192 knots (GRID_HOST_CHUNK).  GRID_HOST_CHUNK_DOUBLING=1: a 2048-knot first chunk, then doubling up to
+    // 32 768 -- measured within 2-3 % either way (profiles/r02u_e2e_sweep.log), so equal chunks stay the default.
+    static const int fixed_chunk = env_int("GRID_HOST_CHUNK_DOUBLING", 0) ? 0 : ((env_int("GRID_HOST_CHUNK", 8192) + 31) / 32) * 32;
     T* d_in = static_cast<T*>(w.d_in);
     T* d_in2 = h_in2 ? static_cast<T*>(w.d_in2) : nullptr;
     T* d_out = static_cast<T*>(w.d_out);
     int i = 0;
-    for (int k0 = 0; k0 < nk; k0 += chunk, i++) {
+    int chunk = fixed_chunk > 0 ? fixed_chunk : 2048;
+    for (int k0 = 0; k0 < nk; k0 += chunk, i++, chunk = fixed_chunk > 0 ? fixed_chunk : (chunk < 32768 ? chunk * 2 : chunk)) {
         const int c = nk - k0 < chunk ? nk - k0 : chunk;
         cudaStream_t st = w.streams[i % 3];
         e = cudaMemcpyAsync(d_in + size_t(k0) * in_per_knot, h_in + size_t(k0) * in_per_knot,

@@ -16,8 +16,9 @@ def main():
     import torch
     from gridcodegenerator_b200.runtime import get_library
     torch.cuda.set_device(0)
-    lib = get_library("iiwa14")
-    n, B = lib.n, int(os.environ.get("E2E_BATCH", "65536"))
+    robot = os.environ.get("E2E_ROBOT", "iiwa14")
+    lib = get_library(robot)
+    n, B = lib.n, int(os.environ.get("E2E_BATCH", "65536" if robot == "iiwa14" else "16384"))
     rng = np.random.default_rng(0)
     h_in = torch.from_numpy(rng.uniform(-1, 1, (B, 3 * n)).astype(np.float32)).pin_memory()
     h_out = torch.empty((B, 2 * n * n), dtype=torch.float32).pin_memory()
@@ -33,7 +34,7 @@ def main():
             lib.forward_dynamics_gradient_host(h_in, h_out)
         torch.cuda.synchronize()
         best = min(best, (time.perf_counter() - t0) / steps)
-    print(json.dumps({"zero_copy": os.environ.get("GRID_HOST_ZEROCOPY", "0"), "chunk": os.environ.get("GRID_HOST_CHUNK", "16384"),
+    print(json.dumps({"robot": robot, "zero_copy": os.environ.get("GRID_HOST_ZEROCOPY", "0"), "chunk": "doubling from 2048" if os.environ.get("GRID_HOST_CHUNK_DOUBLING") == "1" else os.environ.get("GRID_HOST_CHUNK", "8192"),
                       "batch": B, "ms_per_step": best * 1e3, "knots_per_s": B / best,
                       "pcie_GBps": B * (3 * n + 2 * n * n) * 4 / best / 1e9, "matches_device_path": ok}), flush=True)
 
