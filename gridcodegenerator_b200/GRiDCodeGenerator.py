@@ -140,6 +140,7 @@ class GRiDCodeGenerator:
         # device and kernel tiers are emitted together (the kernel is a 6-line shell around the device tier)
         for v in variants or self._variants(key):
             self._add_block(_hdr.emit_device_and_kernel(self._specs[v], self.model.n))
+            self._add_block(_hdr.emit_reference_device(self._specs[v], self.model.n))
 
     def _gen_kernel(self, key: str, variants=None):
         for v in variants or self._variants(key):

@@ -24,6 +24,48 @@ typedef float T;
 static std::vector<T> g_out;
 static void section(const T* p, size_t count) { g_out.insert(g_out.end(), p, p + count); }
 
+// ---- user kernels written against the REFERENCE's device tier (banner GRiDCodeGenerator.py:318-352): one thread block
+// per knot point (grid-strided), inputs and results in shared memory, X_device<T>(s_out, s_q, s_qd, ..., d_robotModel,
+// gravity) called by every thread of the block.  d_x rows are [q | qd | u | qdd].
+constexpr int NJ = NUM_JOINTS;
+template <int WHICH>
+__global__ void user_device_tier(T* d_out, const int out_n, const T* d_x, const T* d_Minv, const robotModel<T>* d_robotModel,
+                                 const T gravity, const int N) {
+    __shared__ T s_x[4 * NJ];
+    __shared__ T s_Minv[NJ * NJ];
+    extern __shared__ T s_out[];
+    const int tid = threadIdx.x + threadIdx.y * blockDim.x, nthreads = blockDim.x * blockDim.y;
+    const T *s_q = s_x, *s_qd = s_x + NJ, *s_u = s_x + 2 * NJ, *s_qdd = s_x + 3 * NJ;
+    for (int k = blockIdx.x; k < N; k += gridDim.x) {
+        for (int i = tid; i < 4 * NJ; i += nthreads) s_x[i] = d_x[size_t(k) * 4 * NJ + i];
+        for (int i = tid; i < NJ * NJ; i += nthreads) s_Minv[i] = d_Minv[size_t(k) * NJ * NJ + i];
+        __syncthreads();
+        if (WHICH == 0) inverse_dynamics_device<T>(s_out, s_q, s_qd, d_robotModel, gravity);
+        if (WHICH == 1) inverse_dynamics_device<T>(s_out, s_q, s_qd, s_qdd, d_robotModel, gravity);
+        if (WHICH == 2) direct_minv_device<T>(s_out, s_q, d_robotModel);
+        if (WHICH == 3) forward_dynamics_device<T>(s_out, s_q, s_qd, s_u, d_robotModel, gravity);
+        if (WHICH == 4) inverse_dynamics_gradient_device<T>(s_out, s_q, s_qd, s_qdd, d_robotModel, gravity);
+        if (WHICH == 5) forward_dynamics_gradient_device<T>(s_out, s_q, s_qd, s_u, d_robotModel, gravity);
+        if (WHICH == 6) forward_dynamics_gradient_device<T>(s_out, s_q, s_qd, s_qdd, s_Minv, d_robotModel, gravity);
+        if (WHICH == 7) end_effector_pose_device<T>(s_out, s_q, d_robotModel);
+        __syncthreads();
+        for (int i = tid; i < out_n; i += nthreads) d_out[size_t(k) * out_n + i] = s_out[i];
+        __syncthreads();
+    }
+}
+template <int WHICH>
+static void run_device_tier(int out_n, const T* d_x, const T* d_Minv, const robotModel<T>* d_robotModel, T gravity, int N) {
+    T* d_out;
+    gpuErrchk(cudaMalloc(&d_out, size_t(N) * out_n * sizeof(T)));
+    gpuErrchk(cudaMemset(d_out, 0, size_t(N) * out_n * sizeof(T)));
+    user_device_tier<WHICH><<<296, dim3(16, 4), out_n * sizeof(T)>>>(d_out, out_n, d_x, d_Minv, d_robotModel, gravity, N);
+    gpuErrchk(cudaGetLastError());
+    std::vector<T> h(size_t(N) * out_n);
+    gpuErrchk(cudaMemcpy(h.data(), d_out, h.size() * sizeof(T), cudaMemcpyDeviceToHost));
+    gpuErrchk(cudaFree(d_out));
+    section(h.data(), h.size());
+}
+
 int main(int argc, char** argv) {
     if (argc < 3) { fprintf(stderr, "usage: %s input.bin output.bin\n", argv[0]); return 2; }
     constexpr int N = HOST_TIER_KNOTS;
@@ -106,6 +148,23 @@ int main(int argc, char** argv) {
     // 15: cumulative joint transforms (the quantity the reference's X_single_thread / X_warp accumulate)
     joint_transforms<T, true>(hd_data, d_robotModel, N, dimms, dimms, streams);
     section(hd_data->h_jointXforms, size_t(N) * 16 * n);
+
+    // 16-23: the reference's DEVICE tier called from block-per-knot user kernels (b1: device tier)
+    {
+        T* d_x;
+        gpuErrchk(cudaMalloc(&d_x, in.size() * sizeof(T)));
+        gpuErrchk(cudaMemcpy(d_x, in.data(), in.size() * sizeof(T), cudaMemcpyHostToDevice));
+        const T* d_Minv = hd_data->d_Minv;                     // left on the device by section 3
+        run_device_tier<0>(n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<1>(n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<2>(n * n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<3>(n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<4>(2 * n * n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<5>(2 * n * n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<6>(2 * n * n, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<7>(6 * NUM_EES, d_x, d_Minv, d_robotModel, gravity, N);
+        gpuErrchk(cudaFree(d_x));
+    }
 
     close_grid<T>(streams, d_robotModel, hd_data);
 

@@ -483,6 +483,39 @@ def emit_device_and_kernel(sp: AlgoSpec, n: int) -> str:
     return dev + ker
 
 
+# algorithms whose reference device tier (banner GRiDCodeGenerator.py:318-352) gets a same-signature entry point here
+REFERENCE_DEVICE_TIER = ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+                         "forward_dynamics_gradient", "end_effector_pose", "end_effector_pose_gradient",
+                         "end_effector_pose_gradient_hessian")
+
+
+def emit_reference_device(sp: AlgoSpec, n: int) -> str:
+    """`X_device<T>(T *s_out, const T *s_q, ..., const robotModel<T> *d_robotModel[, const T gravity])` with the
+    REFERENCE's parameter list and calling convention (shared-memory pointers, one knot point per thread block, every
+    thread of the block calls it; e.g. algorithms/_inverse_dynamics.py:360-386).  User kernels written against the
+    reference's device tier compile and give the right results; the work of the knot is done by the block's first warp
+    running this back end's per-thread body (all its lanes compute the same knot, so the shared-memory results are
+    written consistently), the other warps wait at the barrier.  For throughput use X_kernel / X_launch instead."""
+    if sp.key not in REFERENCE_DEVICE_TIER or sp.fixed_target:
+        return ""
+    ins = "".join(f"const T *s_{p_}, " for p_ in sp.inner_inputs)
+    grav = ", const T gravity" if sp.uses_gravity else ""
+    args = ", ".join(f"s_{p_}" for p_ in sp.inner_inputs)
+    gcall = "gravity" if sp.uses_gravity else "T(0)"
+    return (f"/** Reference-signature device tier of {sp.fn}{sp.tag}: shared-memory pointers, one knot point per thread block,\n"
+            f" *  called by every thread of the block (it synchronises the block before and after).  d_robotModel is accepted\n"
+            f" *  for source compatibility (robot constants are immediates of the code). */\n"
+            f"template <typename T>\n__device__\n"
+            f"void {sp.fn}_device(T *s_out, {ins}const robotModel<T> *d_robotModel{grav}) {{\n"
+            f"    (void)d_robotModel;\n"
+            f"    __syncthreads();\n"
+            f"    if (threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y < 32) {{\n"
+            f"        T S[{algo_struct_name(sp)}<T>::SLOTS];\n"
+            f"        {sp.fn}_inner<T, 1, 1>(s_out, {args}, S, {gcall});\n"
+            f"    }}\n"
+            f"    __syncthreads();\n}}\n\n")
+
+
 def emit_launch(sp: AlgoSpec, n: int) -> str:
     """Stream-asynchronous launcher: persistent grid sized from the occupancy of this kernel."""
     C = f"{sp.fn}{sp.tag}_cfg<T>"

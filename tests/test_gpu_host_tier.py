@@ -69,4 +69,22 @@ def test_host_tier_program_matches_c_abi(name, tmp_path):
         off += w.size
         assert np.array_equal(sec, w), f"{name}: host-tier section {i} differs from the C ABI " \
                                        f"(max abs diff {np.abs(sec - w).max():.3e})"
+    # 16-23: block-per-knot user kernels calling the reference-signature DEVICE tier (X_device<T>(s_out, s_q, ...,
+    # d_robotModel, gravity)): the same per-thread bodies compiled into another kernel -> equal up to fp32 rounding
+    device_tier = [
+        lib.inverse_dynamics(q_qd),                                           # 16
+        lib.inverse_dynamics(q_qd, qdd_in),                                   # 17
+        Minv,                                                                 # 18
+        qdd_fd,                                                               # 19
+        lib.inverse_dynamics_gradient(q_qd, qdd_in),                          # 20
+        fdg,                                                                  # 21
+        lib.forward_dynamics_gradient_qdd_minv(q_qd, qdd_in, Minv),           # 22
+        lib.end_effector_pose(q),                                             # 23
+    ]
+    from conftest import rel_err
+    for i, w in enumerate(device_tier):
+        w = w.cpu().numpy()
+        sec = got[off:off + w.size].reshape(w.shape)
+        off += w.size
+        assert rel_err(sec, w) < 2e-6, f"{name}: device-tier section {16 + i} differs from the C ABI ({rel_err(sec, w):.3e})"
     assert off == got.size
