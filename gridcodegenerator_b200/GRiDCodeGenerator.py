@@ -114,7 +114,7 @@ class GRiDCodeGenerator:
                 if v not in self._sbodies:
                     self._sbodies[v] = _hdr.split_body(sp, self.model)
                 xp = os.environ.get("GRID_SPLIT_XPOSE", "0") == "1"
-                ss = tuple(xp and _hdr.split_ntile(self._sbodies[v], sp, self.model.n, sz) > 1 for sz in (4, 8))
+                ss = tuple(xp and _hdr.split_ntile(self._sbodies[v], sp, self.model.n, sz, b.nslots) > 1 for sz in (4, 8))
             self._add_block(_hdr.emit_config(sp, b, self.model.n, ss))
             if sp.fn == "joint_transforms":
                 # the reference's helper names for the same quantity (algorithms/_eepose_gradient_hessian.py:1226-1398)
@@ -273,7 +273,7 @@ def _scratch_constants(self):
             if _hdr.has_split(sp, self.model.n):      # transposed store of the multi-tile split form
                 if name not in self._sbodies:
                     self._sbodies[name] = _hdr.split_body(sp, self.model)
-                g = _hdr.split_ntile(self._sbodies[name], sp, self.model.n, size)
+                g = _hdr.split_ntile(self._sbodies[name], sp, self.model.n, size, b.nslots)
                 if g > 1 and os.environ.get("GRID_SPLIT_XPOSE", "0") == "1":
                     need = max(need, g * 32 * out)
             if size == 4:

@@ -298,15 +298,19 @@ def split_smem_plan(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int):
     return best or (False, 1, 1, state + ins + 32)
 
 
-def split_ntile(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int) -> int:
-    """Tiles whose published state a split CTA holds at once (grid_rt::tile_loop_split_multi).  1 for robots whose
-    output rows are staged in shared memory (there the split form is the small-batch, latency-first form); for big
-    robots (Atlas), whose split form is the default at every batch size and bound by instruction supply, two tiles
-    when shared memory holds them: every column body fetched from L2 is then executed by two warps at once."""
+def split_ntile(sb: "algos.SplitBody", sp: AlgoSpec, n: int, sizeof: int, mono_slots: Optional[int] = None) -> int:
+    """Tiles whose published state a split CTA holds at once (grid_rt::tile_loop_split_multi).  Two, when shared
+    memory holds them, for robots whose split form is the default at EVERY batch size -- their one-lane-per-knot form
+    would keep its state in the global scratch (mono_slots = its slot count: Atlas, floating-base HyQ), or their
+    output rows do not fit shared memory -- since at size that form is bound by instruction supply and every column
+    body fetched from L2 is then executed by two warps at once.  One for the others: there the split form is the
+    small-batch, latency-first form and keeps its TMA-staged output rows."""
     forced = os.environ.get("GRID_SPLIT_NTILE", "")
     if forced:
         return max(1, int(forced))
-    if split_smem_plan(sb, sp, n, sizeof)[0]:
+    staged = split_smem_plan(sb, sp, n, sizeof)[0]
+    always = mono_slots is not None and not choose_config(max(mono_slots, 1), [e for _, e in sp.streams], sp.out_n(n), sizeof)[1]
+    if staged and not always:
         return 1
     a16 = lambda x: (x + 15) & ~15
     need = lambda g: a16(g * max(sb.nslots, 1) * 32 * sizeof) + sum(a16(g * 32 * e * sizeof) for _, e in sp.streams) + 32
@@ -339,7 +343,7 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
     groups = split_assign(sb)
     na = len(sb.parts)
     nw = max(len(groups), na)
-    if nw % 2 and max(split_ntile(sb, sp, n, 4), split_ntile(sb, sp, n, 8)) > 1:
+    if nw % 2 and max(split_ntile(sb, sp, n, 4, mono_slots), split_ntile(sb, sp, n, 8, mono_slots)) > 1:
         nw += 1                  # the two-tile form pairs the warps (tile_loop_split_multi)
     plan4 = split_smem_plan(sb, sp, n, 4)
     plan8 = split_smem_plan(sb, sp, n, 8)
@@ -352,7 +356,7 @@ def emit_split(sp: AlgoSpec, sb: "algos.SplitBody", n: int, mono_slots: int = 1)
         calls = " ".join(f"{stem}_col{c}<T, NT, OS>(o, S);" for c in g)
         cases.append(f"            case {w}: {calls} break;")
     writes = "GRID_BEFORE_FIRST_OUTPUT" in sb.code
-    g4, g8 = split_ntile(sb, sp, n, 4), split_ntile(sb, sp, n, 8)
+    g4, g8 = split_ntile(sb, sp, n, 4, mono_slots), split_ntile(sb, sp, n, 8, mono_slots)
     xpose = os.environ.get("GRID_SPLIT_XPOSE", "0") == "1"
     mcases = []
     for w in range(0, len(groups), 2):

@@ -28,6 +28,11 @@ CASES = [
     (5, "iiwa14", "idsva_so", 3, 32768),                     # 262144 over 8 GPUs = 32768 per GPU
     (5, "iiwa14", "fdsva_so", 3, 32768),
     (5, "iiwa14", "end_effector_pose_gradient_hessian", 1, 32768),
+    # floating-base HyQ (six-joint chain, 18 DoF) at config 3's batch, and a small MPC-horizon batch
+    (0, "hyq_floating", "forward_dynamics_gradient", 3, 16384),
+    (0, "hyq_floating", "forward_dynamics_gradient", 3, 1024),
+    (0, "hyq_floating", "inverse_dynamics_qdd", 3, 16384),
+    (0, "hyq_floating", "forward_dynamics", 3, 16384),
 ]
 
 
