@@ -77,3 +77,34 @@ def test_generator_api_surface(tmp_path):
                  "idsva_so_host", "end_effector_pose_kernel", "joint_transforms_kernel", "X_single_thread", "X_warp", "forward_dynamics_linearization_kernel", "d_fd_lin", "end_effector_pose_gradient_hessian_kernel",
                  "__ffma2_rn"):
         assert name in txt, name
+
+
+def test_two_tile_split_form_policy_and_column_coverage():
+    """header.split_ntile: robots whose one-lane-per-knot gradient kernels would keep their state in the global scratch
+    (floating-base HyQ here; Atlas) get the two-tile split form in fp32, the others keep one tile with TMA-staged
+    output rows; and phase B of either form runs every derivative column exactly once."""
+    import re
+    from gridcodegenerator_b200 import GRiDCodeGenerator, load_robot
+    from gridcodegenerator_b200.emit import header as hdr
+
+    def algo_struct(text, stem):
+        i = text.index(f"struct {stem}_algo {{")
+        return text[i:text.index("\n};", i)]
+
+    for name, want in (("hyq_floating", (2, 1)), ("hyq", (1, 2)), ("branched6", (1, 1))):     # HyQ fp64: state in the scratch too
+        g = GRiDCodeGenerator(load_robot(name))
+        sp = g._specs["forward_dynamics_gradient"]
+        sb = hdr.split_body(sp, g.model)
+        mono = g._body("forward_dynamics_gradient").nslots
+        assert (hdr.split_ntile(sb, sp, g.model.n, 4, mono), hdr.split_ntile(sb, sp, g.model.n, 8, mono)) == want, name
+        text = hdr.emit_split(sp, sb, g.model.n, mono)
+        body = algo_struct(text, "forward_dynamics_gradient_split")
+        nw = int(re.search(r"static constexpr int NW = (\d+);", body).group(1))
+        assert f"NTILE = sizeof(T) == 4 ? {want[0]} : {want[1]};" in body
+        if max(want) > 1:
+            assert nw % 2 == 0                                          # warps pair up over the two tiles
+        single = body[body.index("void phaseB("):body.index("void phaseB_multi(")]
+        multi = body[body.index("void phaseB_multi("):]
+        for part in (single, multi):
+            cols = sorted(int(c) for c in re.findall(r"_col(\d+)<T, NT, OS>", part))
+            assert cols == list(range(g.model.n)), (name, cols)

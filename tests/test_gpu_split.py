@@ -100,7 +100,7 @@ def test_split_form_fp32(name, B, torch_cuda):
         assert torch.equal(lib.forward_dynamics_gradient(wide[:, :3 * n]), res["1"][0])
 
 
-@pytest.mark.parametrize("name,B", [("iiwa14", 257), ("hyq", 96), ("atlas", 40)])
+@pytest.mark.parametrize("name,B", [("iiwa14", 257), ("hyq", 96), ("hyq", 4810), ("atlas", 40)])   # hyq 4810: 151 tiles, two per pass
 def test_split_form_fp64(name, B, torch_cuda):
     torch = torch_cuda
     lib, orc = _lib(name), _oracle(name)
