@@ -3,6 +3,7 @@ import os
 
 from .model import Robot, Joint, Link, FixedJoint, LinkDesc, JointDesc
 from .urdf import parse_urdf, parse_urdf_string, URDFParser
+from . import floating  # noqa: F401  (pose / twist <-> six-joint-chain coordinates of a floating base)
 
 LIBRARY_DIR = os.path.join(os.path.dirname(__file__), "library")
 _CACHE = {}

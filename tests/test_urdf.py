@@ -224,3 +224,42 @@ def test_floating_joint_in_the_middle_of_a_tree():
     assert names == ["j1", "free_px", "free_py", "free_pz", "free_rx", "free_ry", "free_rz"]
     c = Oracle(r).rnea(np.zeros(7), np.zeros(7), np.zeros(7))[0]
     assert abs(c[3] - 2.0 * G) < 1e-10                               # the z translation carries the payload's weight
+
+
+def test_floating_chain_coordinate_helpers():
+    """robot/floating.py against the model itself: the pose of the chain coordinates is the product of the robot's own
+    homogeneous joint transforms, the twist Jacobian reproduces the base-link velocity the oracle's RNEA computes, the
+    conversions round-trip, and the base wrench of a robot at rest is its weight along world z."""
+    import sympy as sp
+    from gridcodegenerator_b200.robot import floating as fl
+    from gridcodegenerator_b200.robot.model import THETA
+    _, robot = _floating_pair()
+    orc = Oracle(robot)
+    n = robot.get_num_pos()
+    rng = np.random.default_rng(17)
+    hom = [sp.lambdify(THETA, M, "numpy") for M in robot.get_Xmats_hom_ordered_by_id()[:6]]
+    for _ in range(4):
+        q6 = np.concatenate([rng.uniform(-1, 1, 3), rng.uniform(-1.2, 1.2, 3)])
+        T = np.eye(4)
+        for j in range(6):
+            T = T @ np.array(hom[j](q6[j]), dtype=np.float64)
+        p, R = fl.pose_from_chain(q6)
+        assert np.abs(T[:3, 3] - p).max() < 1e-12 and np.abs(T[:3, :3] - R).max() < 1e-12
+        assert np.abs(fl.chain_from_pose(p, R) - q6).max() < 1e-12
+        # quaternion (x, y, z, w) of R by the standard formula -> same coordinates
+        w = 0.5 * np.sqrt(max(1e-16, 1 + np.trace(R)))
+        quat = np.array([(R[2, 1] - R[1, 2]) / (4 * w), (R[0, 2] - R[2, 0]) / (4 * w), (R[1, 0] - R[0, 1]) / (4 * w), w])
+        assert np.abs(fl.chain_from_pose(p, quat) - q6).max() < 1e-10
+        # twist of the base link: column 5 of the oracle's v is the base link's spatial velocity
+        qd6 = rng.uniform(-1, 1, 6)
+        q = np.concatenate([q6, rng.uniform(-1, 1, n - 6)])
+        qd = np.concatenate([qd6, np.zeros(n - 6)])
+        v = orc.rnea(q, qd, np.zeros(n))[1]
+        J = fl.twist_jacobian(q6)
+        assert np.abs(J @ qd6 - v[:, 5]).max() < 1e-10
+        assert np.abs(fl.chain_rates_from_twist(q6, J @ qd6) - qd6).max() < 1e-10
+        # robot at rest: generalized base forces = J^T [moment; force]; the force is the weight along WORLD z
+        c = orc.rnea(q, np.zeros(n), np.zeros(n))[0]
+        wrench = fl.generalized_force_to_wrench(q6, c[:6])
+        mass = 53.433 + 4 * (2.93 + 2.638 + 0.881)
+        assert np.abs(R @ wrench[3:] - np.array([0, 0, mass * G])).max() < 1e-8
