@@ -309,6 +309,7 @@ def gen_add_constants_helpers(self):
               f"const int GRID_SCRATCH_BLOCKS_PER_SM = {1 if per4 * 296 * 4 > (1 << 30) else 2};"]
     self.gen_add_code_lines(lines)
     self._add_block(_sc.STRUCTS)
+    self._add_block(_uh.mx_device_helpers())
 
 
 def gen_add_shared_mem_constants(self):

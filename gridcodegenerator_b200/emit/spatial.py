@@ -169,17 +169,21 @@ class Xform:
         return tm_congruence(em, self.TT, tm_congruence(em, self.TJ, M))
 
 
+# column S of the motion cross-product matrix crm(v) = [[w x, 0], [v_lin x, w x]]: entry i = sign * v[k]
+MXS_TABLE = {
+    0: {1: (1, 2), 2: (-1, 1), 4: (1, 5), 5: (-1, 4)},
+    1: {0: (-1, 2), 2: (1, 0), 3: (-1, 5), 5: (1, 3)},
+    2: {0: (1, 1), 1: (-1, 0), 3: (1, 4), 4: (-1, 3)},
+    3: {4: (1, 2), 5: (-1, 1)},
+    4: {3: (-1, 2), 5: (1, 0)},
+    5: {3: (1, 1), 4: (-1, 0)},
+}
+
+
 def mxS(em: Em, S: int, v: Sequence[V], alpha: Optional[V] = None) -> List[V]:
     """Column S of the motion cross-product matrix of v, times alpha (reference _test.py:522-608)."""
     a = alpha
-    table = {
-        0: {1: (1, 2), 2: (-1, 1), 4: (1, 5), 5: (-1, 4)},
-        1: {0: (-1, 2), 2: (1, 0), 3: (-1, 5), 5: (1, 3)},
-        2: {0: (1, 1), 1: (-1, 0), 3: (1, 4), 4: (-1, 3)},
-        3: {4: (1, 2), 5: (-1, 1)},
-        4: {3: (-1, 2), 5: (1, 0)},
-        5: {3: (1, 1), 4: (-1, 0)},
-    }[S]
+    table = MXS_TABLE[S]
     out = []
     for i in range(6):
         if i in table:

@@ -201,8 +201,59 @@ def gen_topology_sparsity_helpers_python(self, INIT_MODE=False):
     return dva_cols_per_partial, dva_cols_per_jid, running_dva, df_cols_per_partial, df_cols_per_jid, running_df, anc
 
 
+# ------------------------------------------------------------------ motion cross-product columns for user kernels
+def mx_device_helpers() -> str:
+    """C++ text of the reference's device helpers mx<S>[_peq][_scaled]<T>(s_vecX, s_vec[, alpha]) and
+    mxX[_peq][_scaled]<T>(s_vecX, s_vec[, alpha], S_ind) (reference helpers/_spatial_algebra_helpers.py:197-255):
+    s_vecX (=, +=) [alpha *] column S of the motion cross-product matrix of the 6-vector s_vec.  The algorithm bodies
+    of this back end fold these products at emit time (spatial.mxS); the functions exist for user kernels and for
+    gen_mx_func_call_for_cpp.  Generated from the same table (spatial.MXS_TABLE)."""
+    from .spatial import MXS_TABLE
+    out = ["// ---- motion cross-product columns (user-kernel helpers; reference names and argument lists)"]
+    variants = (("", "=", False), ("_peq", "+=", False), ("_scaled", "=", True), ("_peq_scaled", "+=", True))
+    for S in range(6):
+        for suffix, op, scaled in variants:
+            args = "T *s_vecX, const T *s_vec" + (", const T alpha" if scaled else "")
+            body = []
+            for i in range(6):
+                if i in MXS_TABLE[S]:
+                    sg, k = MXS_TABLE[S][i]
+                    val = ("-" if sg < 0 else "") + f"s_vec[{k}]" + ("*alpha" if scaled else "")
+                elif op == "+=":
+                    continue
+                else:
+                    val = "static_cast<T>(0)"
+                body.append(f"s_vecX[{i}] {op} {val};")
+            out.append(f"template <typename T>\n__host__ __device__ __forceinline__\nvoid mx{S}{suffix}({args}) {{ " + " ".join(body) + " }")
+    for suffix, _, scaled in variants:
+        args = "T *s_vecX, const T *s_vec" + (", const T alpha" if scaled else "") + ", const int S_ind"
+        call = "s_vecX, s_vec" + (", alpha" if scaled else "")
+        cases = " ".join(f"case {S}: mx{S}{suffix}<T>({call}); break;" for S in range(6))
+        out.append(f"template <typename T>\n__host__ __device__ __forceinline__\nvoid mxX{suffix}({args}) {{ switch (S_ind) {{ {cases} }} }}")
+    return "\n".join(out) + "\n"
+
+
+def gen_mx_func_call_for_cpp(self, inds=None, PEQ_FLAG=False, SCALE_FLAG=False, updated_var_names=None):
+    """Emit the call of the motion cross-product helper for the joints `inds` (default: all): mx<S> when they share
+    one motion-subspace index S, mxX with the run-time S_ind otherwise.  updated_var_names renames the arguments
+    (keys S_ind_name, s_dst_name, s_src_name, s_scale_name)."""
+    names = dict(S_ind_name="S_ind", s_dst_name="s_dst", s_src_name="s_src", s_scale_name="s_scale")
+    names.update(updated_var_names or {})
+    if inds is None:
+        inds = list(range(self.robot.get_num_pos()))
+    same = self.robot.are_Ss_identical(inds)
+    which = str(int(list(self.robot.get_S_by_id(inds[0])).index(1))) if same else "X"
+    fn = "mx" + which + ("_peq" if PEQ_FLAG else "") + ("_scaled" if SCALE_FLAG else "") + "<T>"
+    args = [names["s_dst_name"], names["s_src_name"]]
+    if SCALE_FLAG:
+        args.append(names["s_scale_name"])
+    if not same:
+        args.append(names["S_ind_name"])
+    self.gen_add_code_line(fn + "(" + ", ".join(args) + ");")
+
+
 PUBLIC = ("gen_add_parallel_loop", "gen_add_serial_ops", "gen_add_sync", "gen_add_debug_print_code_line",
           "gen_add_debug_print_code_lines", "gen_static_array_ind_2d", "gen_static_array_ind_3d", "gen_var_in_list",
           "gen_var_not_in_list", "gen_add_multi_threaded_select", "gen_kernel_load_inputs",
           "gen_kernel_load_inputs_single_timing", "gen_kernel_save_result", "gen_kernel_save_result_single_timing",
-          "gen_topology_sparsity_helpers_python")
+          "gen_topology_sparsity_helpers_python", "gen_mx_func_call_for_cpp")

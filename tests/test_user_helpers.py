@@ -13,9 +13,11 @@ from gridcodegenerator_b200 import GRiDCodeGenerator, load_robot
 
 
 def _user_kernel_source():
+    from gridcodegenerator_b200.emit.user_helpers import mx_device_helpers
     g = GRiDCodeGenerator(load_robot("branched6"))
     g.code_str, g.indent_level = "", 0
     g.gen_add_code_lines(["#include <cstdio>", "#include <cooperative_groups.h>", "namespace cgrps = cooperative_groups;", ""])
+    g.code_str += mx_device_helpers()          # in a generated grid.cuh these come with the header
     g.gen_add_func_doc("y[k] = 2 * x[k] on the first half of every row, 3 * x[k] on the second half; z[k] = sum of row k",
                        ["one thread block per knot point (grid-strided), rows of 12 values"],
                        ["d_y is the output", "d_x is the input", "N is the number of rows"], None)
@@ -51,6 +53,27 @@ def _user_kernel_source():
     g.gen_add_debug_print_code_line('if (false) printf("%f\\n", (double)s_y[0]);', use_thread_group=True)
     g.gen_kernel_save_result_single_timing("y", "12", use_thread_group=True)
     g.gen_add_end_function()
+    # motion cross-product helpers through gen_mx_func_call_for_cpp: fixed S (joint 0 alone) and run-time S (all joints)
+    g.gen_add_code_line("template <typename T>")
+    g.gen_add_code_line("__global__ void user_kernel_mx(T *d_y, const T *d_x, const int S_ind) {", True)
+    g.gen_add_code_line("__shared__ T s_src[6]; __shared__ T s_dst[24];")
+    g.gen_add_parallel_loop("ind", "6")
+    g.gen_add_code_line("s_src[ind] = d_x[ind];")
+    g.gen_add_end_control_flow()
+    g.gen_add_parallel_loop("ind", "24")
+    g.gen_add_code_line("s_dst[ind] = static_cast<T>(1);")
+    g.gen_add_end_control_flow()
+    g.gen_add_sync()
+    g.gen_add_serial_ops()
+    g.gen_add_code_line("const T s_scale = static_cast<T>(0.5);")
+    g.gen_mx_func_call_for_cpp(inds=[0])
+    g.gen_mx_func_call_for_cpp(inds=[0], PEQ_FLAG=True, updated_var_names=dict(s_dst_name="&s_dst[6]"))
+    g.gen_mx_func_call_for_cpp(SCALE_FLAG=True, updated_var_names=dict(s_dst_name="&s_dst[12]"))
+    g.gen_mx_func_call_for_cpp(PEQ_FLAG=True, SCALE_FLAG=True, updated_var_names=dict(s_dst_name="&s_dst[18]"))
+    g.gen_add_end_control_flow()
+    g.gen_add_sync()
+    g.gen_kernel_save_result_single_timing("y", "24", load_from_name="s_dst")
+    g.gen_add_end_function()
     assert g.indent_level == 0
     return g.code_str
 
@@ -79,6 +102,29 @@ int main() {
     for (int i = 0; i < 12; i++) {
         const float a = (i == 0 || i == 11) ? 0.0f : (i < 4 ? 1.0f : (i < 8 ? 2.0f : 3.0f));
         bad += y2[i] != a * x[i < 4 ? 0 : (i < 8 ? 4 : 8)];
+    }
+    {   // user_kernel_mx: [mxS(x), 1 + mxS(x), 0.5 mxS2(x), 1 + 0.5 mxS2(x)] with S = branched6's joint-0 axis and S2 = 4
+        std::vector<float> ym(24);
+        float* dym; cudaMalloc(&dym, 96);
+        user_kernel_mx<float><<<1, 32>>>(dym, dx, 4);
+        cudaDeviceSynchronize();
+        cudaMemcpy(ym.data(), dym, 96, cudaMemcpyDeviceToHost);
+        auto crm = [&](int r, int c) {   // entry (r, c) of the motion cross-product matrix of x[0..5]
+            const float* v = x.data();
+            const float w[3] = {v[0], v[1], v[2]}, l[3] = {v[3], v[4], v[5]};
+            auto skew = [](const float* a, int i, int j) { if (i == j) return 0.0f; const int k = 3 - i - j; const float s = ((j - i + 3) % 3 == 1) ? -1.0f : 1.0f; return s * a[k]; };
+            if (r < 3 && c < 3) return skew(w, r, c);
+            if (r >= 3 && c < 3) return skew(l, r - 3, c);
+            if (r >= 3 && c >= 3) return skew(w, r - 3, c - 3);
+            return 0.0f;
+        };
+        const int S0 = MX_FIXED_S;
+        for (int i = 0; i < 6; i++) {
+            bad += ym[i] != crm(i, S0);
+            bad += ym[6 + i] != 1.0f + crm(i, S0);
+            bad += ym[12 + i] != 0.5f * crm(i, 4);
+            bad += ym[18 + i] != 1.0f + 0.5f * crm(i, 4);
+        }
     }
     printf("bad %d\n", bad);
     return bad != 0;
@@ -134,6 +180,24 @@ def test_topology_sparsity_helpers(name):
         assert tuple(ref.gen_topology_sparsity_helpers_python(INIT_MODE=True)) == tuple(init)
 
 
+def _fixed_S():
+    return int(list(load_robot("branched6").get_S_by_id(0)).index(1))
+
+
+def test_mx_call_generator_text():
+    r = load_robot("branched6")
+    g = GRiDCodeGenerator(r)
+    g.code_str, g.indent_level = "", 0
+    g.gen_mx_func_call_for_cpp(inds=[0])
+    S0 = _fixed_S()
+    assert g.code_str.strip() == f"mx{S0}<T>(s_dst, s_src);"
+    g.code_str = ""
+    mixed = not r.are_Ss_identical(list(range(r.get_num_pos())))
+    g.gen_mx_func_call_for_cpp(PEQ_FLAG=True, SCALE_FLAG=True, updated_var_names=dict(s_scale_name="qd_j"))
+    want = "mxX_peq_scaled<T>(s_dst, s_src, qd_j, S_ind);" if mixed else f"mx{S0}_peq_scaled<T>(s_dst, s_src, qd_j);"
+    assert g.code_str.strip() == want
+
+
 def _nvcc():
     from gridcodegenerator_b200.runtime import _nvcc
     return _nvcc()
@@ -145,7 +209,7 @@ def test_user_kernel_compiles():
         cu = os.path.join(d, "user.cu")
         with open(cu, "w") as f:
             f.write(src + HARNESS)
-        res = subprocess.run([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-c", cu, "-o", os.path.join(d, "user.o")],
+        res = subprocess.run([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", f"-DMX_FIXED_S={_fixed_S()}", "-c", cu, "-o", os.path.join(d, "user.o")],
                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert res.returncode == 0, res.stdout[-3000:]
 
@@ -157,6 +221,6 @@ def test_user_kernel_runs():
         cu, exe = os.path.join(d, "user.cu"), os.path.join(d, "user")
         with open(cu, "w") as f:
             f.write(src + HARNESS)
-        subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", cu, "-o", exe])
+        subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", f"-DMX_FIXED_S={_fixed_S()}", cu, "-o", exe])
         res = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
         assert res.returncode == 0 and "bad 0" in res.stdout, res.stdout
