@@ -207,7 +207,7 @@ def _bind(key: str):
     return temp_mem_size, inner, device, kernel, host, driver, function_call
 
 
-for _key in ("joint_transforms", "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+for _key in ("joint_transforms", "inverse_dynamics", "inverse_dynamics_vaf", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
              "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so",
              "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian"):
     _t, _i, _d, _k, _h, _drv, _fc = _bind(_key)
@@ -239,7 +239,7 @@ for _name in _uh.PUBLIC:
 from .emit import scaffold as _sc  # noqa: E402
 
 ALGO_ORDER = ("joint_transforms", "end_effector_pose", "end_effector_pose_gradient", "end_effector_pose_gradient_hessian",
-              "inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+              "inverse_dynamics", "inverse_dynamics_vaf", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
               "forward_dynamics_gradient", "forward_dynamics_linearization", "aba", "crba", "idsva_so", "fdsva_so")
 
 

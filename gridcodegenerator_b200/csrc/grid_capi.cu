@@ -292,6 +292,13 @@ int inverse_dynamics_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_c, i
                       : grid::inverse_dynamics_launch<T>(d_c, d_q_qd, stride, m, g, nk, st), fn);
 }
 template <typename T>
+int inverse_dynamics_vaf_impl(const T* d_q_qd, int stride, const T* d_qdd, T* d_vaf, int nk, T g, void* s) {
+    GRID_CHECK_ARGS("grid_inverse_dynamics_vaf", nk < 0 || stride < 2 * N || (nk > 0 && (!d_q_qd || !d_vaf)),
+                    grid::inverse_dynamics_vaf_cfg<T>::NEEDS_SCRATCH || grid::inverse_dynamics_vaf_qdd_cfg<T>::NEEDS_SCRATCH);
+    return fail(d_qdd ? grid::inverse_dynamics_vaf_qdd_launch<T>(d_vaf, d_q_qd, stride, d_qdd, m, g, nk, st)
+                      : grid::inverse_dynamics_vaf_launch<T>(d_vaf, d_q_qd, stride, m, g, nk, st), fn);
+}
+template <typename T>
 int direct_minv_impl(const T* d_q, int stride, T* d_Minv, int nk, void* s) {
     GRID_CHECK_ARGS("grid_direct_minv", nk < 0 || stride < N || (nk > 0 && (!d_q || !d_Minv)), grid::direct_minv_cfg<T>::NEEDS_SCRATCH);
     return fail(grid::direct_minv_launch<T>(d_Minv, d_q, stride, m, nk, st), fn);
@@ -322,6 +329,8 @@ long info_core(int algo, int what) {
     long grid_capi_info_core_##SUF(int algo, int what) { return info_core<T>(algo, what); }                        \
     extern "C" int grid_inverse_dynamics_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) {      \
         return inverse_dynamics_impl<T>(a, st, b, o, nk, g, s); }                                                  \
+    extern "C" int grid_inverse_dynamics_vaf_##SUF(const T* a, int st, const T* b, T* o, int nk, T g, void* s) {  \
+        return inverse_dynamics_vaf_impl<T>(a, st, b, o, nk, g, s); }                                              \
     extern "C" int grid_direct_minv_##SUF(const T* a, int st, T* o, int nk, void* s) {                             \
         return direct_minv_impl<T>(a, st, o, nk, s); }                                                             \
     extern "C" int grid_forward_dynamics_##SUF(const T* a, int st, T* o, int nk, T g, void* s) {                   \
@@ -337,7 +346,7 @@ int grid_num_joints(void) { return N; }
 int grid_num_ees(void) { return grid::NUM_EES; }
 const char* grid_robot_name(void) { return GRID_ROBOT_NAME; }
 const char* grid_last_error(void) { return grid_capi_last_error().c_str(); }
-int grid_abi_version(void) { return 6; }
+int grid_abi_version(void) { return 7; }
 int grid_has_second_order(void) { return GRID_HAS_SECOND_ORDER; }
 int grid_has_ee_hessian(void) { return GRID_HAS_EE_HESSIAN; }
 const char* grid_fixed_target_name(void) { return GRID_FIXED_TARGET_NAME; }

@@ -48,6 +48,7 @@ __global__ void user_device_tier(T* d_out, const int out_n, const T* d_x, const 
         if (WHICH == 5) forward_dynamics_gradient_device<T>(s_out, s_q, s_qd, s_u, d_robotModel, gravity);
         if (WHICH == 6) forward_dynamics_gradient_device<T>(s_out, s_q, s_qd, s_qdd, s_Minv, d_robotModel, gravity);
         if (WHICH == 7) end_effector_pose_device<T>(s_out, s_q, d_robotModel);
+        if (WHICH == 8) inverse_dynamics_vaf_device<T>(s_out, s_q, s_qd, s_qdd, d_robotModel, gravity);
         __syncthreads();
         for (int i = tid; i < out_n; i += nthreads) d_out[size_t(k) * out_n + i] = s_out[i];
         __syncthreads();
@@ -149,7 +150,7 @@ int main(int argc, char** argv) {
     joint_transforms<T, true>(hd_data, d_robotModel, N, dimms, dimms, streams);
     section(hd_data->h_jointXforms, size_t(N) * 16 * n);
 
-    // 16-23: the reference's DEVICE tier called from block-per-knot user kernels (b1: device tier)
+    // 16-24: the reference's DEVICE tier called from block-per-knot user kernels (b1: device tier)
     {
         T* d_x;
         gpuErrchk(cudaMalloc(&d_x, in.size() * sizeof(T)));
@@ -163,6 +164,7 @@ int main(int argc, char** argv) {
         run_device_tier<5>(2 * n * n, d_x, d_Minv, d_robotModel, gravity, N);
         run_device_tier<6>(2 * n * n, d_x, d_Minv, d_robotModel, gravity, N);
         run_device_tier<7>(6 * NUM_EES, d_x, d_Minv, d_robotModel, gravity, N);
+        run_device_tier<8>(18 * n, d_x, d_Minv, d_robotModel, gravity, N);
         gpuErrchk(cudaFree(d_x));
     }
 

@@ -128,7 +128,7 @@ class Pusher:
 
 # ====================================================================== RNEA
 def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: bool, fname: str = "f", joints=None,
-                 keep_Iv: bool = True):
+                 keep_Iv: bool = True, on_va=None):
     """v, a, f per joint in id order (ids are topologically sorted).  f_j -> state `fname`; with `keep`
     also v_j, I v_j and X a_parent (needed by the gradient).  `joints`: restrict to the joints of some base-rooted
     trees (they do not interact with the rest of a fixed-base robot)."""
@@ -173,12 +173,14 @@ def rnea_forward(cx: Ctx, qd: Sequence[V], qdd: Optional[Sequence[V]], keep: boo
         elif j in nonadj_parent:
             em.store_vec("v", j, v)
             em.store_vec("a", j, a)
+        if on_va is not None:
+            on_va(j, v, a)
         V_[j], A_[j] = v, a
         V_.pop(j - 2, None)
         A_.pop(j - 2, None)
 
 
-def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f", joints=None) -> List[V]:
+def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f", joints=None, on_f=None) -> List[V]:
     """f_parent += X^T f, c_j = S^T f_j + damping qd_j (reference _test.py:78-107)."""
     em, m = cx.em, cx.m
     ps = Pusher(em, fname)
@@ -193,6 +195,8 @@ def rnea_backward(cx: Ctx, qd: Sequence[V], keep_f: bool, fname: str = "f", join
         f = ps.pull(j)
         if keep_f:
             em.store_vec(fname, j, f)
+        if on_f is not None:
+            on_f(j, f)
         c[j] = em.lincomb([(1.0, f[jd.S]), (jd.damping, qd[j])])
         if jd.parent >= 0:
             ps.push(jd.parent, j, lambda acc, f=f, j=j: cx.X[j].applyT(em, f, acc=acc))
@@ -770,6 +774,30 @@ class Body:
         self.code = cx.em.code()
         self.nslots = cx.em.nslots
         self.n_ops = cx.em.n_ops
+
+
+def body_inverse_dynamics_vaf(model: Model, use_qdd: bool) -> Body:
+    """RNEA's spatial velocities, accelerations and (accumulated) forces per joint: the reference's s_vaf array,
+    [v (6n) | a (6n) | f (6n)], 6-vector of joint j at 6 j (inverse_dynamics_inner_vaf, algorithms/_inverse_dynamics.py
+    :33-321; oracle _test.py:5-107, which returns the same three arrays)."""
+    cx = Ctx(model)
+    cx.prologue()
+    em, n = cx.em, model.n
+    qd = cx.read_vec("qd", "qd_")
+    qdd = cx.read_vec("qdd", "qdd_") if use_qdd else None
+
+    def on_va(j, v, a):
+        for r in range(6):
+            _out(em, 6 * j + r, v[r])
+            _out(em, 6 * n + 6 * j + r, a[r])
+
+    def on_f(j, f):
+        for r in range(6):
+            _out(em, 12 * n + 6 * j + r, f[r])
+
+    rnea_forward(cx, qd, qdd, keep=False, on_va=on_va)
+    rnea_backward(cx, qd, keep_f=False, on_f=on_f)
+    return Body("inverse_dynamics_vaf_inner", "", cx, "RNEA v, a, f per joint: [v | a | f], 6 n values each")
 
 
 def body_inverse_dynamics(model: Model, use_qdd: bool) -> Body:

@@ -81,6 +81,11 @@ def specs(n: int, num_ees: int = 1, max_tree: Optional[int] = None, fixed_target
                  ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_c", lambda n: n),
         AlgoSpec("inverse_dynamics", "inverse_dynamics", "ID", "_qdd", lambda m: algos.body_inverse_dynamics(m, True),
                  ["q", "qd", "qdd"], [("d_q_qd", 2 * n), ("d_qdd", n)], [(0, 0), (0, n), (1, 0)], "d_c", lambda n: n),
+        # RNEA's per-joint v, a, f (reference inverse_dynamics_inner_vaf / inverse_dynamics_vaf_device)
+        AlgoSpec("inverse_dynamics_vaf", "inverse_dynamics_vaf", "ID_VAF", "", lambda m: algos.body_inverse_dynamics_vaf(m, False),
+                 ["q", "qd"], [("d_q_qd", 2 * n)], [(0, 0), (0, n)], "d_vaf", lambda n: 18 * n),
+        AlgoSpec("inverse_dynamics_vaf", "inverse_dynamics_vaf", "ID_VAF", "_qdd", lambda m: algos.body_inverse_dynamics_vaf(m, True),
+                 ["q", "qd", "qdd"], [("d_q_qd", 2 * n), ("d_qdd", n)], [(0, 0), (0, n), (1, 0)], "d_vaf", lambda n: 18 * n),
         AlgoSpec("direct_minv", "direct_minv", "MINV", "", algos.body_direct_minv,
                  ["q"], [("d_q", n)], [(0, 0)], "d_Minv", lambda n: n * n, uses_gravity=False),
         AlgoSpec("forward_dynamics", "forward_dynamics", "FD", "", algos.body_forward_dynamics,
@@ -488,7 +493,7 @@ def emit_device_and_kernel(sp: AlgoSpec, n: int) -> str:
 
 
 # algorithms whose reference device tier (banner GRiDCodeGenerator.py:318-352) gets a same-signature entry point here
-REFERENCE_DEVICE_TIER = ("inverse_dynamics", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
+REFERENCE_DEVICE_TIER = ("inverse_dynamics", "inverse_dynamics_vaf", "direct_minv", "forward_dynamics", "inverse_dynamics_gradient",
                          "forward_dynamics_gradient", "end_effector_pose", "end_effector_pose_gradient",
                          "end_effector_pose_gradient_hessian")
 

@@ -240,6 +240,7 @@ class GRiDLibrary:
         vp, ci = ctypes.c_void_p, ctypes.c_int
         for suf, g in (("f32", ctypes.c_float), ("f64", ctypes.c_double)):
             getattr(L, f"grid_inverse_dynamics_{suf}").argtypes = [vp, ci, vp, vp, ci, g, vp]
+            getattr(L, f"grid_inverse_dynamics_vaf_{suf}").argtypes = [vp, ci, vp, vp, ci, g, vp]
             getattr(L, f"grid_direct_minv_{suf}").argtypes = [vp, ci, vp, ci, vp]
             getattr(L, f"grid_forward_dynamics_{suf}").argtypes = [vp, ci, vp, ci, g, vp]
             getattr(L, f"grid_inverse_dynamics_gradient_{suf}").argtypes = [vp, ci, vp, vp, ci, g, vp]
@@ -336,6 +337,22 @@ class GRiDLibrary:
                 raise ValueError("qdd must be a dense (B, n) tensor")
         with torch.cuda.device(q_qd.device):
             self._check(getattr(self.lib, f"grid_inverse_dynamics_{suf}")(p, stride, pq, out.data_ptr(), B, gravity, self._stream()))
+        return out
+
+    def inverse_dynamics_vaf(self, q_qd, qdd=None, gravity: float = 9.81, out=None):
+        """RNEA's per-joint v, a, f: (B, 18 n) = [v | a | f], the 6-vector of joint j at 6 j of each block."""
+        import torch
+        n = self.n
+        p, stride, B = self._dev(q_qd, 2 * n)
+        suf = self._suf(q_qd)
+        out = self._out(out, q_qd, B, 18 * n)
+        pq = None
+        if qdd is not None:
+            pq, sq, Bq = self._dev(qdd, n)
+            if sq != n or Bq != B:
+                raise ValueError("qdd must be a dense (B, n) tensor")
+        with torch.cuda.device(q_qd.device):
+            self._check(getattr(self.lib, f"grid_inverse_dynamics_vaf_{suf}")(p, stride, pq, out.data_ptr(), B, gravity, self._stream()))
         return out
 
     def direct_minv(self, q, out=None):

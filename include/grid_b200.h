@@ -52,6 +52,15 @@ int grid_inverse_dynamics_f32(const float *d_q_qd, int stride, const float *d_qd
 int grid_inverse_dynamics_f64(const double *d_q_qd, int stride, const double *d_qdd, double *d_c, int num_knots,
                               double gravity, void *stream);
 
+/* ---- RNEA's per-joint spatial velocity, acceleration and (accumulated) force
+ * replaces inverse_dynamics_inner_vaf / inverse_dynamics_vaf_device (algorithms/_inverse_dynamics.py:33-321; banner
+ * GRiDCodeGenerator.py:326-329): the reference's s_vaf array per knot, [v (6n) | a (6n) | f (6n)], the 6-vector
+ * ([angular; linear]) of joint j at offset 6 j of each block.  Inputs as grid_inverse_dynamics; d_vaf: 18n per knot. */
+int grid_inverse_dynamics_vaf_f32(const float *d_q_qd, int stride, const float *d_qdd, float *d_vaf, int num_knots,
+                                  float gravity, void *stream);
+int grid_inverse_dynamics_vaf_f64(const double *d_q_qd, int stride, const double *d_qdd, double *d_vaf, int num_knots,
+                                  double gravity, void *stream);
+
 /* ---- direct inverse mass matrix, dense symmetric n x n per knot
  * replaces direct_minv<T,USE_COMPRESSED_MEM> (algorithms/_direct_minv.py:527-588) */
 int grid_direct_minv_f32(const float *d_q, int stride, float *d_Minv, int num_knots, void *stream);

@@ -27,7 +27,7 @@ def test_library_exports_header_symbols(name):
     lib.grid_robot_name.restype = ctypes.c_char_p
     assert lib.grid_robot_name().decode() == name
     assert lib.grid_num_joints() == 2
-    assert lib.grid_abi_version() == 6
+    assert lib.grid_abi_version() == 7
     assert lib.grid_num_ees() == 1 and lib.grid_has_second_order() == 1
     lib.grid_kernel_info.restype = ctypes.c_long
     smem = lib.grid_kernel_info(6, 0, 0)

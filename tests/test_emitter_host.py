@@ -23,6 +23,9 @@ def test_emitted_bodies_match_reference_golden(name, golden, tmp_path):
         cm = lambda M: np.asarray(M).T.reshape(-1)  # column-major flatten
         assert rel_err([call(lib, gen, "inverse_dynamics", n, q, qd)], [g_["c0"][k]]) < TOL
         assert rel_err([call(lib, gen, "inverse_dynamics_qdd", n, q, qd, qdd)], [g_["c"][k]]) < TOL
+        # RNEA's per-joint v, a, f: the reference's s_vaf layout [v | a | f], 6-vector of joint j at 6 j (golden: (6, n))
+        vaf = np.concatenate([np.asarray(g_[key][k]).T.reshape(-1) for key in ("v", "a", "f")])
+        assert rel_err([call(lib, gen, "inverse_dynamics_vaf_qdd", 18 * n, q, qd, qdd)], [vaf]) < TOL
         assert rel_err([call(lib, gen, "direct_minv", n * n, q)], [cm(g_["Minv"][k])]) < TOL
         assert rel_err([call(lib, gen, "inverse_dynamics_gradient", 2 * n * n, q, qd)], [cm(g_["dc_du0"][k])]) < TOL
         assert rel_err([call(lib, gen, "inverse_dynamics_gradient_qdd", 2 * n * n, q, qd, qdd)], [cm(g_["dc_du"][k])]) < TOL

@@ -69,7 +69,7 @@ def test_host_tier_program_matches_c_abi(name, tmp_path):
         off += w.size
         assert np.array_equal(sec, w), f"{name}: host-tier section {i} differs from the C ABI " \
                                        f"(max abs diff {np.abs(sec - w).max():.3e})"
-    # 16-23: block-per-knot user kernels calling the reference-signature DEVICE tier (X_device<T>(s_out, s_q, ...,
+    # 16-24: block-per-knot user kernels calling the reference-signature DEVICE tier (X_device<T>(s_out, s_q, ...,
     # d_robotModel, gravity)): the same per-thread bodies compiled into another kernel -> equal up to fp32 rounding
     device_tier = [
         lib.inverse_dynamics(q_qd),                                           # 16
@@ -80,6 +80,7 @@ def test_host_tier_program_matches_c_abi(name, tmp_path):
         fdg,                                                                  # 21
         lib.forward_dynamics_gradient_qdd_minv(q_qd, qdd_in, Minv),           # 22
         lib.end_effector_pose(q),                                             # 23
+        lib.inverse_dynamics_vaf(q_qd, qdd_in),                               # 24: [v | a | f] per joint
     ]
     from conftest import rel_err
     for i, w in enumerate(device_tier):

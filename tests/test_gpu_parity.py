@@ -65,6 +65,9 @@ def test_golden_vectors(name, dtype, tol, golden, torch_cuda):
     assert rel_err(f(lib.inverse_dynamics(q_qd)), g["c0"]) < tol
     assert rel_err(f(lib.inverse_dynamics(q_qd, qdd)), g["c"]) < tol
     assert rel_err(f(lib.inverse_dynamics(q_qd_u)), g["c0"]) < tol            # strided q_qd_u buffer
+    # RNEA's per-joint v, a, f (the reference's s_vaf; golden arrays are (K, 6, n) -> [v | a | f], 6-vector of joint j at 6 j)
+    vaf = np.concatenate([g[k_].transpose(0, 2, 1).reshape(len(x), -1) for k_ in ("v", "a", "f")], axis=1)
+    assert rel_err(f(lib.inverse_dynamics_vaf(q_qd, qdd)), vaf) < tol
     assert rel_err(f(lib.direct_minv(q)), _cm(g["Minv"])) < tol
     assert rel_err(f(lib.inverse_dynamics_gradient(q_qd)), _cm(g["dc_du0"])) < tol
     assert rel_err(f(lib.inverse_dynamics_gradient(q_qd, qdd)), _cm(g["dc_du"])) < tol
