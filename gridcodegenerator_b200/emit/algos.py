@@ -1683,7 +1683,7 @@ def _publish_state(cx: Ctx, qd: Sequence[V], extra=(), joints=None):
     pending = []
     if em.regs_only:
         for key in keys:
-            if key in em.const_slots:
+            if key in em.const_slots or key not in em.reg_state:       # already a state slot (hybrid state)
                 continue
             pending.append((key, em.reg_state[key]))
         em.regs_only = False

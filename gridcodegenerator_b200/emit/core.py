@@ -16,6 +16,10 @@ from typing import Dict, List, Optional, Sequence, Tuple, Union
 Number = Union[int, float]
 # a lockstep barrier (GRID_SYNC) at every SYNC_EVERY-th section marker of the emitted bodies (0 = none)
 SYNC_EVERY = int(os.environ.get("GRID_SYNC_EVERY", "8"))
+# Hybrid state of the register-resident (small-robot) bodies: state keys whose first element is listed here live in
+# per-thread shared-memory slots instead of registers (A/B knob, e.g. "f,L,Dinv2"): fewer registers per thread buys
+# more resident warps per SM, and a pass over the body costs the same however many warps share it
+HYBRID_KEYS = frozenset(k for k in os.environ.get("GRID_HYBRID_KEYS", "").split(",") if k)
 
 
 class V:
@@ -489,7 +493,7 @@ class Em:
         if self.frozen:
             raise ValueError(f"store to shared state {key} from a read-only (column) emitter")
         self.const_slots.pop(key, None)
-        if self.regs_only:
+        if self.regs_only and key[0] not in HYBRID_KEYS:
             self.reg_state[key] = v
             return
         if v.p:
@@ -512,7 +516,7 @@ class Em:
             return self.reg_state[key]
         if key in self.const_slots:
             return const(self.const_slots[key])
-        if self.regs_only:
+        if self.regs_only and key in self.reg_state:
             return self.reg_state[key]
         if key not in self.slots and (key + ("x",)) in self.slots:
             ix, iy = self.slots[key + ("x",)], self.slots[key + ("y",)]

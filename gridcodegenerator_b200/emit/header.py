@@ -148,6 +148,10 @@ def choose_config(slots: int, in_elems: List[int], out_elems: int, sizeof: int):
     One CTA per SM with as many warps as shared memory (per-thread state + per-warp TMA staging) and the
     register file allow.  The warps of the CTA run in lockstep through the straight-line body (GRID_SYNC points),
     which is what keeps the kernel off the instruction-fetch limit."""
+    forced = os.environ.get("GRID_FORCE_LANE_CONFIG", "")      # A/B: "NT,STATE_SMEM,STAGED" for bodies with state slots
+    if forced and slots > 1:
+        nt_, st_, sg_ = (int(x) for x in forced.split(","))
+        return nt_, bool(st_), sg_
     a16 = lambda x: (x + 15) & ~15
     state_w = a16(slots * 32 * sizeof)
     best = None
